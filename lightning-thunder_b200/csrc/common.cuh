@@ -1,0 +1,190 @@
+// Shared device helpers for the b200k kernels (sm_100a only).
+//
+// Every kernel in this library is HBM-bound: the helpers here exist to (1) move 16 bytes per
+// thread per instruction with streaming cache hints, (2) convert between the storage type and
+// fp32 with round-to-nearest-even exactly where the reference's trace rounds, and (3) reduce
+// across a warp / CTA with shuffles and one shared-memory hop.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200k.h"
+
+namespace b200k {
+
+constexpr int kWarp = 32;
+
+// ---------------------------------------------------------------------------------------------
+// 16-byte global memory access with cache hints.
+//   ld_stream : read-once data (activations).  Non-coherent path, do not allocate in L1.
+//   ld_keep   : small re-used vectors (weights, cos/sin).  Default caching.
+//   st_stream : write-once outputs.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 ld_stream(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint4 ld_keep(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void st_stream(void* p, const uint4& v) {
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Storage-type traits: a 16-byte vector holds kElems elements of T.
+// unpack(): storage -> fp32 (exact).  pack(): fp32 -> storage (round-to-nearest-even).
+// rnd(): round an fp32 value through the storage type and back (a trace-level rounding point).
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+struct Vec;
+
+template <>
+struct Vec<float> {
+    static constexpr int kElems = 4;
+    static constexpr int kDtype = B200K_F32;
+    __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+        f[0] = __uint_as_float(v.x);
+        f[1] = __uint_as_float(v.y);
+        f[2] = __uint_as_float(v.z);
+        f[3] = __uint_as_float(v.w);
+    }
+    __device__ static __forceinline__ uint4 pack(const float* f) {
+        return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+    }
+    __device__ static __forceinline__ float rnd(float x) { return x; }
+    __device__ static __forceinline__ float load1(const void* p, int64_t i) { return reinterpret_cast<const float*>(p)[i]; }
+    __device__ static __forceinline__ void store1(void* p, int64_t i, float x) { reinterpret_cast<float*>(p)[i] = x; }
+};
+
+template <>
+struct Vec<__nv_bfloat16> {
+    static constexpr int kElems = 8;
+    static constexpr int kDtype = B200K_BF16;
+    __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            f[2 * i] = __uint_as_float(w[i] << 16);
+            f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
+    }
+    __device__ static __forceinline__ uint4 pack(const float* f) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            __nv_bfloat162 p = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+            w[i] = *reinterpret_cast<uint32_t*>(&p);
+        }
+        return make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    __device__ static __forceinline__ float rnd(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+    __device__ static __forceinline__ float load1(const void* p, int64_t i) {
+        return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
+    }
+    __device__ static __forceinline__ void store1(void* p, int64_t i, float x) {
+        reinterpret_cast<__nv_bfloat16*>(p)[i] = __float2bfloat16_rn(x);
+    }
+};
+
+template <>
+struct Vec<__half> {
+    static constexpr int kElems = 8;
+    static constexpr int kDtype = B200K_F16;
+    __device__ static __forceinline__ void unpack(const uint4& v, float* f) {
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float2 p = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+            f[2 * i] = p.x;
+            f[2 * i + 1] = p.y;
+        }
+    }
+    __device__ static __forceinline__ uint4 pack(const float* f) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            __half2 p = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+            w[i] = *reinterpret_cast<uint32_t*>(&p);
+        }
+        return make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    __device__ static __forceinline__ float rnd(float x) { return __half2float(__float2half_rn(x)); }
+    __device__ static __forceinline__ float load1(const void* p, int64_t i) {
+        return __half2float(reinterpret_cast<const __half*>(p)[i]);
+    }
+    __device__ static __forceinline__ void store1(void* p, int64_t i, float x) {
+        reinterpret_cast<__half*>(p)[i] = __float2half_rn(x);
+    }
+};
+
+// ---------------------------------------------------------------------------------------------
+// Reductions.
+// ---------------------------------------------------------------------------------------------
+struct SumOp {
+    __device__ __forceinline__ float operator()(float a, float b) const { return a + b; }
+};
+struct MaxOp {
+    __device__ __forceinline__ float operator()(float a, float b) const { return fmaxf(a, b); }
+};
+
+template <int kLanes = 32, typename Op>
+__device__ __forceinline__ float warp_reduce(float v, Op op) {
+#pragma unroll
+    for (int o = kLanes / 2; o > 0; o >>= 1) v = op(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Reduce kVals independent values across a CTA of kThreads threads in one shared-memory hop.
+// `smem` must hold kVals * (kThreads / 32) floats and must not be in use by another reduction
+// that has not passed its trailing __syncthreads (callers alternate two buffers instead).
+// Every thread gets the result.
+template <int kThreads, int kVals, typename Op>
+__device__ __forceinline__ void block_reduce(float (&v)[kVals], float* smem, Op op, float identity) {
+    constexpr int kWarps = kThreads / kWarp;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < kVals; ++i) v[i] = warp_reduce(v[i], op);
+    if constexpr (kWarps > 1) {
+        if (lane == 0) {
+#pragma unroll
+            for (int i = 0; i < kVals; ++i) smem[i * kWarps + warp] = v[i];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < kVals; ++i) {
+            float x = lane < kWarps ? smem[i * kWarps + lane] : identity;
+            v[i] = warp_reduce<(kWarps > 1 ? kWarps : 2)>(x, op);
+            v[i] = __shfl_sync(0xffffffffu, v[i], 0);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Host-side helpers.
+// ---------------------------------------------------------------------------------------------
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+inline int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+inline int launch_status() {
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : static_cast<int>(e);
+}
+
+}  // namespace b200k
