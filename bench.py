@@ -173,25 +173,37 @@ def load_peaks():
 
 
 class ClockSampler:
-    FIELDS = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    FIELDS = "timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index):
         self.index, self.proc, self.path = index, None, None
+        self.t_load0 = self.t_load1 = None
 
     def start(self):
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
+    def mark_load(self, begin):
+        if begin:
+            self.t_load0 = time.time()
+        else:
+            self.t_load1 = time.time()
+
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        """Median SM clock and any throttle reason seen while the GPU was under this benchmark's load
+        (timed steps + per-kernel loops + e2e steps)."""
+        import datetime
+
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "window": "timed steps + per-kernel loops + e2e steps"}
         if self.proc is None:
             return out
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -201,13 +213,17 @@ class ClockSampler:
         try:
             for line in open(self.path):
                 f = [c.strip() for c in line.split(",")]
-                if len(f) < 7:
+                if len(f) < 8:
                     continue
                 try:
-                    sm.append(float(f[0])), smax.append(float(f[1]))
+                    ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                    clk, cmax = float(f[1]), float(f[2])
                 except ValueError:
                     continue
-                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if self.t_load0 is not None and (ts < self.t_load0 - 0.02 or ts > (self.t_load1 or time.time()) + 0.02):
+                    continue
+                sm.append(clk), smax.append(cmax)
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
                     if val.lower().startswith("active"):
                         reasons.add(name)
             os.unlink(self.path)
@@ -291,8 +307,8 @@ def run_reference_arm(args, wl):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="rmsnorm", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -326,16 +342,17 @@ def main():
     from b200ex import _lib
 
     _lib.lib()  # fail loudly before timing anything if the CUDA library is missing
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()  # nvidia-smi needs ~1 s to start printing; allocation + warm-up cover that
     wl.alloc(device)
     stream = torch.cuda.current_stream(device)
 
     # ---- whole-step throughput, inputs resident in HBM ------------------------------------------
     for i in range(args.warmup):
         wl.step(i)
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
     barrier()
+    sampler.mark_load(True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     for i in range(args.steps):
@@ -349,7 +366,7 @@ def main():
 
     # ---- per-kernel timing for the roofline (same process, CUDA events on the launch stream) ------
     kernels = []
-    kiters = max(20, min(args.steps, 100))
+    kiters = max(200, min(args.steps, 2000))
     for name, fn, nbytes in wl.kernels():
         for i in range(3):
             fn(i)
@@ -362,14 +379,13 @@ def main():
         torch.cuda.synchronize(device)
         us = a.elapsed_time(b) * 1e3 / kiters
         kernels.append({"kernel": name, "us_per_launch": us, "algorithmic_bytes": nbytes, "achieved_gbps": nbytes / us / 1e3})
-    clocks = sampler.stop() if rank == 0 else None
 
     # ---- end to end with host buffers ---------------------------------------------------------
     e2e = None
     if not args.no_e2e:
         host = wl.host_inputs(99 + rank, pin=True)
         out_host = wl.e2e_out_host()
-        e2e_steps = max(3, min(args.steps, 10))
+        e2e_steps = max(3, min(args.steps, 20))
         for _ in range(2):
             wl.e2e_step(host, device, out_host)
         barrier()
@@ -388,6 +404,8 @@ def main():
                "ms_per_step": ems.item() / e2e_steps, "steps": e2e_steps,
                "api": "b200ex.ops.rmsnorm_fwd/rmsnorm_bwd on pinned host tensors (H2D + launch + D2H per step)"}
 
+    sampler.mark_load(False)
+    clocks = sampler.stop() if rank == 0 else None
     if rank == 0:
         peak, peak_src = load_peaks()
         dom = max(kernels, key=lambda k: k["us_per_launch"])

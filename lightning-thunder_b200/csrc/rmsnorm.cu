@@ -7,6 +7,8 @@
 // forward; dy, h, dh_in -> dx backward.  The backward keeps per-thread fp32 partial sums of dw for
 // the columns it owns across all rows the (persistent) CTA processes, writes one partial row per
 // CTA to scratch, and a second tiny kernel folds the partials (deterministic, no atomics).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200k {
@@ -276,6 +278,208 @@ rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ h, const T* _
     }
 }
 
+// -------------------------------------------------------------------------------------------
+// Backward, TMA-staged: the streaming variant used whenever a row group fits shared memory.
+//
+// One producer warp keeps a ring of kStages row groups in flight with 1-D bulk copies
+// (cp.async.bulk -> mbarrier complete_tx); the consumer threads (blockDim.x - 32 of them, thread t
+// owns 16-byte vectors t, t + nc, ...) read their columns from shared memory, so the number of bytes
+// in flight per SM is set by the ring (up to ~200 KB), not by registers or occupancy.  dx goes
+// straight from registers to global memory.  Consumers synchronise among themselves on named
+// barrier 1 only; the producer never joins.
+// Stage layout: [dy rows | h rows | dh_in rows], each kRows * row_bytes.
+// -------------------------------------------------------------------------------------------
+constexpr int kProducerThreads = 32;
+
+template <typename T, int kVpl, int kRows, bool kHasW, bool kHasDhIn>
+__global__ void __launch_bounds__(512 / kVpl + kProducerThreads, kVpl >= 2 ? 2 : 1)
+rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const T* __restrict__ w,
+                       const float* __restrict__ rstd, const T* __restrict__ dh_in, T* __restrict__ dx,
+                       float* __restrict__ dw_partial, int64_t rows, int nvec, float hidden_f, int stages) {
+    using V = Vec<T>;
+    constexpr int kE = V::kElems;
+    constexpr bool kIsF32 = V::kDtype == B200K_F32;
+    constexpr int kTensors = kHasDhIn ? 3 : 2;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t row_bytes = static_cast<uint32_t>(nvec) * 16u;
+    const uint32_t group_bytes = row_bytes * kRows;          // one tensor's rows in a stage
+    const uint32_t stage_bytes = group_bytes * kTensors;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);  // [stages]
+    uint64_t* empty = full + stages;                         // [stages]
+    float* red = reinterpret_cast<float*>(empty + stages);   // [2][kRows][32]
+    unsigned char* ring = smem_raw + ((2 * stages * 8 + 2 * kRows * 32 * 4 + 127) / 128) * 128;
+
+    const int nc = blockDim.x - kProducerThreads;  // consumer threads
+    const int ncw = nc >> 5;
+    const int tid = threadIdx.x;
+    const int64_t ngroups = (rows + kRows - 1) / kRows;
+
+    if (tid == 0) {
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], ncw);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    if (tid >= nc) {
+        // ===== producer warp: one elected lane issues all copies =====
+        if (tid == nc) {
+            const uint64_t pol = policy_evict_first();
+            int s = 0;
+            uint32_t phase = 0;
+            for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
+                mbar_wait(&empty[s], phase ^ 1u);
+                const int64_t row0 = g * kRows;
+                const int64_t live = rows - row0 < kRows ? rows - row0 : kRows;
+                const uint32_t bytes = static_cast<uint32_t>(live) * row_bytes;
+                unsigned char* st = ring + static_cast<size_t>(s) * stage_bytes;
+                mbar_arrive_expect_tx(&full[s], bytes * kTensors);
+                const size_t goff = static_cast<size_t>(row0) * row_bytes;
+                bulk_g2s(st, reinterpret_cast<const unsigned char*>(dy) + goff, bytes, &full[s], pol);
+                bulk_g2s(st + group_bytes, reinterpret_cast<const unsigned char*>(h) + goff, bytes, &full[s], pol);
+                if constexpr (kHasDhIn)
+                    bulk_g2s(st + 2 * group_bytes, reinterpret_cast<const unsigned char*>(dh_in) + goff, bytes, &full[s], pol);
+                if (++s == stages) {
+                    s = 0;
+                    phase ^= 1u;
+                }
+            }
+        }
+        return;
+    }
+
+    // ===== consumers =====
+    const int lane = tid & 31, warp = tid >> 5;
+    uint4 wv[kVpl];
+    float dwacc[kVpl][kE];
+#pragma unroll
+    for (int i = 0; i < kVpl; ++i) {
+        const int v = tid + i * nc;
+        if constexpr (kHasW) wv[i] = v < nvec ? ld_keep(reinterpret_cast<const uint4*>(w) + v) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int e = 0; e < kE; ++e) dwacc[i][e] = 0.f;
+    }
+
+    int s = 0;
+    uint32_t phase = 0;
+    int parity = 0;
+    for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x, parity ^= 1) {
+        const int64_t row0 = g * kRows;
+        float rs[kRows];
+#pragma unroll
+        for (int r = 0; r < kRows; ++r) rs[r] = row0 + r < rows ? rstd[row0 + r] : 0.f;
+
+        mbar_wait(&full[s], phase);
+        const unsigned char* st = ring + static_cast<size_t>(s) * stage_bytes;
+
+        uint4 dyv[kRows][kVpl], hv[kRows][kVpl], div[kRows][kVpl];
+#pragma unroll
+        for (int r = 0; r < kRows; ++r) {
+            const bool live = row0 + r < rows;
+#pragma unroll
+            for (int i = 0; i < kVpl; ++i) {
+                const int v = tid + i * nc;
+                const bool ok = live && v < nvec;
+                const uint32_t off = static_cast<uint32_t>(r) * row_bytes + static_cast<uint32_t>(v) * 16u;
+                dyv[r][i] = ok ? lds128(st + off) : make_uint4(0, 0, 0, 0);
+                hv[r][i] = ok ? lds128(st + group_bytes + off) : make_uint4(0, 0, 0, 0);
+                if constexpr (kHasDhIn) div[r][i] = ok ? lds128(st + 2 * group_bytes + off) : make_uint4(0, 0, 0, 0);
+            }
+        }
+        // Everything this warp needs from the stage is now in registers: hand the slot back.
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+        if (++s == stages) {
+            s = 0;
+            phase ^= 1u;
+        }
+
+        float c[kRows];
+#pragma unroll
+        for (int r = 0; r < kRows; ++r) {
+            float acc = 0.f;
+#pragma unroll
+            for (int i = 0; i < kVpl; ++i) {
+                float dyf[kE], hf[kE], wf[kE];
+                V::unpack(dyv[r][i], dyf);
+                V::unpack(hv[r][i], hf);
+                if constexpr (kHasW) V::unpack(wv[i], wf);
+#pragma unroll
+                for (int e = 0; e < kE; ++e) acc += hf[e] * (kHasW ? wf[e] * dyf[e] : dyf[e]);
+            }
+            c[r] = warp_reduce(acc, SumOp{});
+        }
+        if (ncw > 1) {
+            float* rb = red + parity * (kRows * 32);
+            if (lane == 0) {
+#pragma unroll
+                for (int r = 0; r < kRows; ++r) rb[r * 32 + warp] = c[r];
+            }
+            named_bar_sync(1, nc);
+#pragma unroll
+            for (int r = 0; r < kRows; ++r) {
+                float xsum = lane < ncw ? rb[r * 32 + lane] : 0.f;
+                c[r] = warp_reduce(xsum, SumOp{});
+            }
+        }
+
+#pragma unroll
+        for (int r = 0; r < kRows; ++r) {
+            const int64_t row = row0 + r;
+            if (row >= rows) break;
+            const float rstd_r = rs[r];
+            const float sc = ((-0.5f * c[r]) * (rstd_r * rstd_r * rstd_r)) / hidden_f;
+#pragma unroll
+            for (int i = 0; i < kVpl; ++i) {
+                const int v = tid + i * nc;
+                float dyf[kE], hf[kE], wf[kE], o[kE];
+                V::unpack(dyv[r][i], dyf);
+                V::unpack(hv[r][i], hf);
+                if constexpr (kHasW) V::unpack(wv[i], wf);
+#pragma unroll
+                for (int e = 0; e < kE; ++e) {
+                    const float gg = kHasW ? wf[e] * dyf[e] : dyf[e];
+                    const float hs = hf[e] * sc;
+                    o[e] = rstd_r * gg;
+                    o[e + 0] = kHasDhIn && kIsF32 ? o[e] : (o[e] + hs) + hs;
+                    if constexpr (kHasW) dwacc[i][e] += V::rnd((hf[e] * rstd_r) * dyf[e]);
+                }
+                if constexpr (kHasDhIn) {
+                    float df[kE];
+                    V::unpack(div[r][i], df);
+#pragma unroll
+                    for (int e = 0; e < kE; ++e) {
+                        if constexpr (kIsF32) {
+                            const float hs = hf[e] * sc;
+                            o[e] = ((df[e] + o[e]) + hs) + hs;
+                        } else {
+                            o[e] = df[e] + V::rnd(o[e]);
+                        }
+                    }
+                }
+                if (v < nvec) st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + v, V::pack(o));
+            }
+        }
+    }
+
+    if constexpr (kHasW) {
+        float* prow = dw_partial + static_cast<int64_t>(blockIdx.x) * nvec * kE;
+#pragma unroll
+        for (int i = 0; i < kVpl; ++i) {
+            const int v = tid + i * nc;
+            if (v < nvec) {
+#pragma unroll
+                for (int q = 0; q < kE / 4; ++q) {
+                    reinterpret_cast<float4*>(prow + static_cast<int64_t>(v) * kE)[q] =
+                        make_float4(dwacc[i][4 * q], dwacc[i][4 * q + 1], dwacc[i][4 * q + 2], dwacc[i][4 * q + 3]);
+                }
+            }
+        }
+    }
+}
+
 // dw[col] = round_T(sum_g partial[g][col]).  Block = 32 columns x 8 row slices.
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -427,6 +631,34 @@ int dispatch_fwd(const void* x, const void* res, const void* w, void* h_out, voi
 
 constexpr int kBwdRows = 2;
 
+// Backward tuning knobs, read once from the environment (A/B measurements only):
+//   B200K_RMSNORM_BWD_TMA=0      use the register-resident kernel instead of the TMA-staged one
+//   B200K_RMSNORM_BWD_VPL=1|2|4  16-byte vectors per consumer thread
+//   B200K_RMSNORM_BWD_ROWS=1|2   rows per pipeline stage
+//   B200K_RMSNORM_BWD_CTAS=1|2   resident CTAs per SM (splits the shared-memory ring)
+struct TmaTune {
+    bool enabled;
+    int vpl, rows, ctas_per_sm;
+};
+TmaTune tma_tune() {
+    static TmaTune t = [] {
+        auto geti = [](const char* name, int dflt) {
+            const char* e = getenv(name);
+            return e != nullptr && e[0] != 0 ? atoi(e) : dflt;
+        };
+        TmaTune r;
+        r.enabled = geti("B200K_RMSNORM_BWD_TMA", 1) != 0;
+        r.vpl = geti("B200K_RMSNORM_BWD_VPL", 1);
+        r.rows = geti("B200K_RMSNORM_BWD_ROWS", 2);
+        r.ctas_per_sm = geti("B200K_RMSNORM_BWD_CTAS", 1);
+        if (r.vpl != 1 && r.vpl != 2 && r.vpl != 4) r.vpl = 1;
+        if (r.rows != 1 && r.rows != 2) r.rows = 2;
+        if (r.ctas_per_sm < 1 || r.ctas_per_sm > kBwdCtasPerSm) r.ctas_per_sm = 1;
+        return r;
+    }();
+    return t;
+}
+
 template <typename T, bool kHasW, bool kHasDhIn>
 int launch_bwd(const void* dy, const void* h, const void* w, const float* rstd, const void* dh_in, void* dx, void* dw,
                void* scratch, int64_t scratch_bytes, int64_t rows, int64_t hidden, cudaStream_t st) {
@@ -450,6 +682,50 @@ int launch_bwd(const void* dy, const void* h, const void* w, const float* rstd, 
     if (kHasW && (scratch == nullptr || !aligned16(scratch) || scratch_bytes < b200k_rmsnorm_bwd_scratch_bytes(rows, hidden)))
         return B200K_ESCRATCH;
     int grid = 0;
+    {
+        // TMA-staged streaming kernel.  Tunables (env, read once): consumer vectors per thread, rows per
+        // stage, CTAs per SM.  Defaults are the measured best for [8192 x 4096] bf16 on B200.
+        const TmaTune t = tma_tune();
+        int rc = -1000;
+        auto try_tma = [&](auto kernel, int vpl, int kr) {
+            constexpr int kTensors = kHasDhIn ? 3 : 2;
+            const int64_t stage_bytes = nvec * 16 * kr * kTensors;
+            const int64_t budget = (t.ctas_per_sm >= 2 ? 100 : 200) * 1024;
+            int64_t stages = budget / stage_bytes;
+            if (stages > 8) stages = 8;
+            int64_t cthreads = (nvec + vpl - 1) / vpl;
+            cthreads = (cthreads + 31) / 32 * 32;
+            if (stages < 2 || cthreads > 512 / vpl || cthreads < 32) return;
+            const size_t smem = ((2 * stages * 8 + 2 * kr * 32 * 4 + 127) / 128) * 128 + stages * stage_bytes;
+            cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+            if (e != cudaSuccess) {
+                rc = static_cast<int>(e);
+                return;
+            }
+            const int64_t groups = (rows + kr - 1) / kr;
+            const int64_t cap = static_cast<int64_t>(sm_count()) * t.ctas_per_sm;
+            grid = static_cast<int>(groups < cap ? groups : cap);
+            kernel<<<grid, static_cast<int>(cthreads) + kProducerThreads, smem, st>>>(
+                static_cast<const T*>(dy), static_cast<const T*>(h), static_cast<const T*>(w), rstd, static_cast<const T*>(dh_in),
+                static_cast<T*>(dx), static_cast<float*>(scratch), rows, static_cast<int>(nvec), static_cast<float>(hidden),
+                static_cast<int>(stages));
+            rc = launch_status();
+        };
+        if (t.enabled) {
+            if (t.vpl == 1 && t.rows == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 1, 1, kHasW, kHasDhIn>, 1, 1);
+            else if (t.vpl == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 1, 2, kHasW, kHasDhIn>, 1, 2);
+            else if (t.vpl == 2 && t.rows == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 2, 1, kHasW, kHasDhIn>, 2, 1);
+            else if (t.vpl == 2) try_tma(rmsnorm_bwd_tma_kernel<T, 2, 2, kHasW, kHasDhIn>, 2, 2);
+            else if (t.rows == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 4, 1, kHasW, kHasDhIn>, 4, 1);
+            else try_tma(rmsnorm_bwd_tma_kernel<T, 4, 2, kHasW, kHasDhIn>, 4, 2);
+        }
+        if (rc != -1000) {
+            if (rc != 0 || !kHasW) return rc;
+            rmsnorm_dw_reduce_kernel<T><<<static_cast<int>((hidden + 31) / 32), 256, 0, st>>>(
+                static_cast<const float*>(scratch), static_cast<T*>(dw), grid, hidden);
+            return launch_status();
+        }
+    }
     auto go = [&](auto kernel) {
         grid = persistent_grid(kernel, p.threads, (rows + kBwdRows - 1) / kBwdRows, kBwdCtasPerSm);
         kernel<<<grid, p.threads, 0, st>>>(static_cast<const T*>(dy), static_cast<const T*>(h), static_cast<const T*>(w), rstd,

@@ -33,8 +33,12 @@ def _check(x, r, w, dy, dh, eps, what):
     scale = (edx.float() - dh.float()).abs() if dh is not None else None
     assert_parity(dx, edx, what=what + " dx", ulp_scale=scale)
     if w is not None:
-        # dw sums `rows` storage-rounded terms in fp32; the order differs from ATen's.
-        assert_parity(dw, edw, what=what + " dw")
+        # dw sums `rows` storage-rounded terms in fp32 in a different order than ATen: the error is bounded
+        # by ulps of the sum of |terms| (a cancelling column can have |dw| far below that), not of |dw|.
+        # In 16-bit storage a last-bit difference in h*rstd can also flip the rounding of one term by an ulp.
+        terms = ((eh.float() * erstd) * dy.float()).to(x.dtype).float().abs()
+        scale = terms.sum(0) * 4.0 if x.dtype == torch.float32 else terms.max(0).values + terms.sum(0) * 2.0**-12
+        assert_parity(dw, edw, what=what + " dw", ulp_scale=scale)
     else:
         assert dw is None
 
