@@ -58,6 +58,7 @@ struct Vec<float> {
         return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
     }
     __device__ static __forceinline__ float rnd(float x) { return x; }
+    __device__ static __forceinline__ void rnd2(float&, float&) {}
     __device__ static __forceinline__ float load1(const void* p, int64_t i) { return reinterpret_cast<const float*>(p)[i]; }
     __device__ static __forceinline__ void store1(void* p, int64_t i, float x) { reinterpret_cast<float*>(p)[i] = x; }
 };
@@ -84,6 +85,13 @@ struct Vec<__nv_bfloat16> {
         return make_uint4(w[0], w[1], w[2], w[3]);
     }
     __device__ static __forceinline__ float rnd(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+    // Round a pair through bf16 with one packed conversion (F2FP, full rate) instead of two F2F.
+    __device__ static __forceinline__ void rnd2(float& a, float& b) {
+        __nv_bfloat162 p = __floats2bfloat162_rn(a, b);
+        const uint32_t u = *reinterpret_cast<uint32_t*>(&p);
+        a = __uint_as_float(u << 16);
+        b = __uint_as_float(u & 0xffff0000u);
+    }
     __device__ static __forceinline__ float load1(const void* p, int64_t i) {
         return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
     }
@@ -115,6 +123,11 @@ struct Vec<__half> {
         return make_uint4(w[0], w[1], w[2], w[3]);
     }
     __device__ static __forceinline__ float rnd(float x) { return __half2float(__float2half_rn(x)); }
+    __device__ static __forceinline__ void rnd2(float& a, float& b) {
+        const float2 r = __half22float2(__floats2half2_rn(a, b));
+        a = r.x;
+        b = r.y;
+    }
     __device__ static __forceinline__ float load1(const void* p, int64_t i) {
         return __half2float(reinterpret_cast<const __half*>(p)[i]);
     }

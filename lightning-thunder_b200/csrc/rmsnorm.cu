@@ -279,23 +279,23 @@ rmsnorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ h, const T* _
 }
 
 // -------------------------------------------------------------------------------------------
-// Backward, TMA-staged: the streaming variant used whenever a row group fits shared memory.
+// Backward, TMA-staged: the streaming variant used whenever a row group fits shared memory and
+// blockDim.x * kVpl == nvec exactly (no column predicates in the hot loop).
 //
-// One producer warp keeps a ring of kStages row groups in flight with 1-D bulk copies
-// (cp.async.bulk -> mbarrier complete_tx); the consumer threads (blockDim.x - 32 of them, thread t
-// owns 16-byte vectors t, t + nc, ...) read their columns from shared memory, so the number of bytes
-// in flight per SM is set by the ring (up to ~200 KB), not by registers or occupancy.  dx goes
-// straight from registers to global memory.  Consumers synchronise among themselves on named
-// barrier 1 only; the producer never joins.
+// A ring of `stages` row groups is kept in flight with 1-D bulk copies (cp.async.bulk -> mbarrier
+// complete_tx), so the bytes in flight per SM are set by the ring (up to ~200 KB), not by registers
+// or occupancy.  Thread t owns the 16-byte vectors t, t + blockDim.x, ...; it reads them from shared
+// memory, hands the slot back (one mbarrier arrive per warp) and thread 0 refills it right after the
+// CTA-wide reduction barrier, at which point every warp is known to have released it.  dx goes
+// straight from registers to global memory.
 // Stage layout: [dy rows | h rows | dh_in rows], each kRows * row_bytes.
 // -------------------------------------------------------------------------------------------
-constexpr int kProducerThreads = 32;
-
 template <typename T, int kVpl, int kRows, bool kHasW, bool kHasDhIn>
-__global__ void __launch_bounds__(512 / kVpl + kProducerThreads, kVpl >= 2 ? 2 : 1)
+__global__ void __launch_bounds__(512 / kVpl, kVpl >= 2 ? 2 : 1)
 rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const T* __restrict__ w,
                        const float* __restrict__ rstd, const T* __restrict__ dh_in, T* __restrict__ dx,
-                       float* __restrict__ dw_partial, int64_t rows, int nvec, float hidden_f, int stages) {
+                       float* __restrict__ dw_partial, int64_t rows, int nvec, float hidden_f, float inv_hidden_exact,
+                       int stages) {
     using V = Vec<T>;
     constexpr int kE = V::kElems;
     constexpr bool kIsF32 = V::kDtype == B200K_F32;
@@ -309,10 +309,25 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
     float* red = reinterpret_cast<float*>(empty + stages);   // [2][kRows][32]
     unsigned char* ring = smem_raw + ((2 * stages * 8 + 2 * kRows * 32 * 4 + 127) / 128) * 128;
 
-    const int nc = blockDim.x - kProducerThreads;  // consumer threads
+    const int nc = blockDim.x;
     const int ncw = nc >> 5;
     const int tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
     const int64_t ngroups = (rows + kRows - 1) / kRows;
+    uint64_t pol = 0;
+
+    auto issue = [&](int64_t g, int s) {
+        const int64_t row0 = g * kRows;
+        const int64_t live = rows - row0 < kRows ? rows - row0 : kRows;
+        const uint32_t bytes = static_cast<uint32_t>(live) * row_bytes;
+        unsigned char* st = ring + static_cast<size_t>(s) * stage_bytes;
+        mbar_arrive_expect_tx(&full[s], bytes * kTensors);
+        const size_t goff = static_cast<size_t>(row0) * row_bytes;
+        bulk_g2s(st, reinterpret_cast<const unsigned char*>(dy) + goff, bytes, &full[s], pol);
+        bulk_g2s(st + group_bytes, reinterpret_cast<const unsigned char*>(h) + goff, bytes, &full[s], pol);
+        if constexpr (kHasDhIn)
+            bulk_g2s(st + 2 * group_bytes, reinterpret_cast<const unsigned char*>(dh_in) + goff, bytes, &full[s], pol);
+    };
 
     if (tid == 0) {
         for (int s = 0; s < stages; ++s) {
@@ -320,47 +335,25 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
             mbar_init(&empty[s], ncw);
         }
         mbar_fence_init();
+        pol = policy_evict_first();
+        for (int s = 0; s < stages; ++s) {
+            const int64_t g = blockIdx.x + static_cast<int64_t>(s) * gridDim.x;
+            if (g < ngroups) issue(g, s);
+        }
     }
     __syncthreads();
 
-    if (tid >= nc) {
-        // ===== producer warp: one elected lane issues all copies =====
-        if (tid == nc) {
-            const uint64_t pol = policy_evict_first();
-            int s = 0;
-            uint32_t phase = 0;
-            for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
-                mbar_wait(&empty[s], phase ^ 1u);
-                const int64_t row0 = g * kRows;
-                const int64_t live = rows - row0 < kRows ? rows - row0 : kRows;
-                const uint32_t bytes = static_cast<uint32_t>(live) * row_bytes;
-                unsigned char* st = ring + static_cast<size_t>(s) * stage_bytes;
-                mbar_arrive_expect_tx(&full[s], bytes * kTensors);
-                const size_t goff = static_cast<size_t>(row0) * row_bytes;
-                bulk_g2s(st, reinterpret_cast<const unsigned char*>(dy) + goff, bytes, &full[s], pol);
-                bulk_g2s(st + group_bytes, reinterpret_cast<const unsigned char*>(h) + goff, bytes, &full[s], pol);
-                if constexpr (kHasDhIn)
-                    bulk_g2s(st + 2 * group_bytes, reinterpret_cast<const unsigned char*>(dh_in) + goff, bytes, &full[s], pol);
-                if (++s == stages) {
-                    s = 0;
-                    phase ^= 1u;
-                }
-            }
-        }
-        return;
-    }
-
-    // ===== consumers =====
-    const int lane = tid & 31, warp = tid >> 5;
-    uint4 wv[kVpl];
+    float wf[kVpl][kE];
     float dwacc[kVpl][kE];
 #pragma unroll
     for (int i = 0; i < kVpl; ++i) {
-        const int v = tid + i * nc;
-        if constexpr (kHasW) wv[i] = v < nvec ? ld_keep(reinterpret_cast<const uint4*>(w) + v) : make_uint4(0, 0, 0, 0);
+        if constexpr (kHasW) V::unpack(ld_keep(reinterpret_cast<const uint4*>(w) + tid + i * nc), wf[i]);
 #pragma unroll
         for (int e = 0; e < kE; ++e) dwacc[i][e] = 0.f;
     }
+
+    // Let the dependent dw-reduce grid be scheduled early; it blocks in griddepcontrol.wait until this grid is done.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     int s = 0;
     uint32_t phase = 0;
@@ -377,24 +370,17 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
         uint4 dyv[kRows][kVpl], hv[kRows][kVpl], div[kRows][kVpl];
 #pragma unroll
         for (int r = 0; r < kRows; ++r) {
-            const bool live = row0 + r < rows;
 #pragma unroll
             for (int i = 0; i < kVpl; ++i) {
-                const int v = tid + i * nc;
-                const bool ok = live && v < nvec;
-                const uint32_t off = static_cast<uint32_t>(r) * row_bytes + static_cast<uint32_t>(v) * 16u;
-                dyv[r][i] = ok ? lds128(st + off) : make_uint4(0, 0, 0, 0);
-                hv[r][i] = ok ? lds128(st + group_bytes + off) : make_uint4(0, 0, 0, 0);
-                if constexpr (kHasDhIn) div[r][i] = ok ? lds128(st + 2 * group_bytes + off) : make_uint4(0, 0, 0, 0);
+                const uint32_t off = static_cast<uint32_t>(r) * row_bytes + static_cast<uint32_t>(tid + i * nc) * 16u;
+                dyv[r][i] = lds128(st + off);
+                hv[r][i] = lds128(st + group_bytes + off);
+                if constexpr (kHasDhIn) div[r][i] = lds128(st + 2 * group_bytes + off);
             }
         }
         // Everything this warp needs from the stage is now in registers: hand the slot back.
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);
-        if (++s == stages) {
-            s = 0;
-            phase ^= 1u;
-        }
 
         float c[kRows];
 #pragma unroll
@@ -402,12 +388,11 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
             float acc = 0.f;
 #pragma unroll
             for (int i = 0; i < kVpl; ++i) {
-                float dyf[kE], hf[kE], wf[kE];
+                float dyf[kE], hf[kE];
                 V::unpack(dyv[r][i], dyf);
                 V::unpack(hv[r][i], hf);
-                if constexpr (kHasW) V::unpack(wv[i], wf);
 #pragma unroll
-                for (int e = 0; e < kE; ++e) acc += hf[e] * (kHasW ? wf[e] * dyf[e] : dyf[e]);
+                for (int e = 0; e < kE; ++e) acc += hf[e] * (kHasW ? wf[i][e] * dyf[e] : dyf[e]);
             }
             c[r] = warp_reduce(acc, SumOp{});
         }
@@ -417,12 +402,25 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
 #pragma unroll
                 for (int r = 0; r < kRows; ++r) rb[r * 32 + warp] = c[r];
             }
-            named_bar_sync(1, nc);
+            __syncthreads();
 #pragma unroll
             for (int r = 0; r < kRows; ++r) {
                 float xsum = lane < ncw ? rb[r * 32 + lane] : 0.f;
-                c[r] = warp_reduce(xsum, SumOp{});
+                c[r] = warp_reduce<16>(xsum, SumOp{});
+                c[r] = __shfl_sync(0xffffffffu, c[r], 0);
             }
+        }
+        // Every warp has released slot s (its arrive precedes the barrier above): refill it.
+        if (tid == 0) {
+            const int64_t gn = g + static_cast<int64_t>(stages) * gridDim.x;
+            if (gn < ngroups) {
+                mbar_wait(&empty[s], phase);
+                issue(gn, s);
+            }
+        }
+        if (++s == stages) {
+            s = 0;
+            phase ^= 1u;
         }
 
 #pragma unroll
@@ -430,36 +428,49 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
             const int64_t row = row0 + r;
             if (row >= rows) break;
             const float rstd_r = rs[r];
-            const float sc = ((-0.5f * c[r]) * (rstd_r * rstd_r * rstd_r)) / hidden_f;
+            const float t3 = (-0.5f * c[r]) * (rstd_r * rstd_r * rstd_r);
+            // t3 / hidden; a multiply by the exact reciprocal when hidden is a power of two (bit-identical).
+            const float sc = inv_hidden_exact != 0.f ? t3 * inv_hidden_exact : t3 / hidden_f;
 #pragma unroll
             for (int i = 0; i < kVpl; ++i) {
-                const int v = tid + i * nc;
-                float dyf[kE], hf[kE], wf[kE], o[kE];
+                float dyf[kE], hf[kE], o[kE], dwt[kE];
                 V::unpack(dyv[r][i], dyf);
                 V::unpack(hv[r][i], hf);
-                if constexpr (kHasW) V::unpack(wv[i], wf);
 #pragma unroll
                 for (int e = 0; e < kE; ++e) {
-                    const float gg = kHasW ? wf[e] * dyf[e] : dyf[e];
+                    const float gg = kHasW ? wf[i][e] * dyf[e] : dyf[e];
                     const float hs = hf[e] * sc;
                     o[e] = rstd_r * gg;
                     o[e + 0] = kHasDhIn && kIsF32 ? o[e] : (o[e] + hs) + hs;
-                    if constexpr (kHasW) dwacc[i][e] += V::rnd((hf[e] * rstd_r) * dyf[e]);
+                    if constexpr (kHasW) dwt[e] = (hf[e] * rstd_r) * dyf[e];
+                }
+                if constexpr (kHasW) {
+#pragma unroll
+                    for (int e = 0; e < kE; e += 2) {
+                        V::rnd2(dwt[e], dwt[e + 1]);
+                        dwacc[i][e] += dwt[e];
+                        dwacc[i][e + 1] += dwt[e + 1];
+                    }
                 }
                 if constexpr (kHasDhIn) {
                     float df[kE];
                     V::unpack(div[r][i], df);
+                    if constexpr (kIsF32) {
 #pragma unroll
-                    for (int e = 0; e < kE; ++e) {
-                        if constexpr (kIsF32) {
+                        for (int e = 0; e < kE; ++e) {
                             const float hs = hf[e] * sc;
                             o[e] = ((df[e] + o[e]) + hs) + hs;
-                        } else {
-                            o[e] = df[e] + V::rnd(o[e]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < kE; e += 2) {
+                            V::rnd2(o[e], o[e + 1]);
+                            o[e] += df[e];
+                            o[e + 1] += df[e + 1];
                         }
                     }
                 }
-                if (v < nvec) st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + v, V::pack(o));
+                st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, V::pack(o));
             }
         }
     }
@@ -469,36 +480,65 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
 #pragma unroll
         for (int i = 0; i < kVpl; ++i) {
             const int v = tid + i * nc;
-            if (v < nvec) {
 #pragma unroll
-                for (int q = 0; q < kE / 4; ++q) {
-                    reinterpret_cast<float4*>(prow + static_cast<int64_t>(v) * kE)[q] =
-                        make_float4(dwacc[i][4 * q], dwacc[i][4 * q + 1], dwacc[i][4 * q + 2], dwacc[i][4 * q + 3]);
-                }
+            for (int q = 0; q < kE / 4; ++q) {
+                reinterpret_cast<float4*>(prow + static_cast<int64_t>(v) * kE)[q] =
+                    make_float4(dwacc[i][4 * q], dwacc[i][4 * q + 1], dwacc[i][4 * q + 2], dwacc[i][4 * q + 3]);
             }
         }
     }
 }
 
-// dw[col] = round_T(sum_g partial[g][col]).  Block = 32 columns x 8 row slices.
+// dw[col] = round_T(sum_g partial[g][col]).  CTA = 16 float4 column groups (64 columns) x 16 part slices;
+// every thread has all of its (nparts / 16) 16-byte loads in flight at once, so the kernel costs about
+// one L2 round trip.  Launched with programmatic stream serialization: griddepcontrol.wait holds it
+// until the producing grid has completed and flushed, so its launch latency hides under that grid.
 template <typename T>
 __global__ void __launch_bounds__(256)
 rmsnorm_dw_reduce_kernel(const float* __restrict__ partial, T* __restrict__ dw, int nparts, int64_t hidden) {
-    __shared__ float tile[8][kWarp + 1];
-    const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
-    const int64_t col = static_cast<int64_t>(blockIdx.x) * 32 + cx;
-    float acc = 0.f;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    __shared__ float4 tile[16][17];
+    const int cx = threadIdx.x & 15, ry = threadIdx.x >> 4;
+    const int64_t col = (static_cast<int64_t>(blockIdx.x) * 16 + cx) * 4;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     if (col < hidden) {
-        for (int g = ry; g < nparts; g += 8) acc += partial[static_cast<int64_t>(g) * hidden + col];
+#pragma unroll 4
+        for (int g = ry; g < nparts; g += 16) {
+            const float4 v = *reinterpret_cast<const float4*>(partial + static_cast<int64_t>(g) * hidden + col);
+            acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+        }
     }
     tile[ry][cx] = acc;
     __syncthreads();
     if (ry == 0 && col < hidden) {
-        float s = 0.f;
+        float4 t = tile[0][cx];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) s += tile[k][cx];
-        Vec<T>::store1(dw, col, s);
+        for (int k = 1; k < 16; ++k) {
+            const float4 v = tile[k][cx];
+            t.x += v.x, t.y += v.y, t.z += v.z, t.w += v.w;
+        }
+        Vec<T>::store1(dw, col, t.x);
+        Vec<T>::store1(dw, col + 1, t.y);
+        Vec<T>::store1(dw, col + 2, t.z);
+        Vec<T>::store1(dw, col + 3, t.w);
     }
+}
+
+template <typename T>
+int launch_dw_reduce(const void* scratch, void* dw, int nparts, int64_t hidden, cudaStream_t st) {
+    // hidden is a multiple of 4 on every path that reaches here (vectorised kernels only).
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>((hidden + 63) / 64));
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, rmsnorm_dw_reduce_kernel<T>, static_cast<const float*>(scratch), static_cast<T*>(dw), nparts, hidden);
+    return e == cudaSuccess ? launch_status() : static_cast<int>(e);
 }
 
 // Generic backward (any hidden): CTA per row for dx, then a column kernel for dw that re-reads h, dy.
@@ -633,7 +673,7 @@ constexpr int kBwdRows = 2;
 
 // Backward tuning knobs, read once from the environment (A/B measurements only):
 //   B200K_RMSNORM_BWD_TMA=0      use the register-resident kernel instead of the TMA-staged one
-//   B200K_RMSNORM_BWD_VPL=1|2|4  16-byte vectors per consumer thread
+//   B200K_RMSNORM_BWD_VPL=1|2    16-byte vectors per thread
 //   B200K_RMSNORM_BWD_ROWS=1|2   rows per pipeline stage
 //   B200K_RMSNORM_BWD_CTAS=1|2   resident CTAs per SM (splits the shared-memory ring)
 struct TmaTune {
@@ -651,7 +691,7 @@ TmaTune tma_tune() {
         r.vpl = geti("B200K_RMSNORM_BWD_VPL", 1);
         r.rows = geti("B200K_RMSNORM_BWD_ROWS", 2);
         r.ctas_per_sm = geti("B200K_RMSNORM_BWD_CTAS", 1);
-        if (r.vpl != 1 && r.vpl != 2 && r.vpl != 4) r.vpl = 1;
+        if (r.vpl != 1 && r.vpl != 2) r.vpl = 1;
         if (r.rows != 1 && r.rows != 2) r.rows = 2;
         if (r.ctas_per_sm < 1 || r.ctas_per_sm > kBwdCtasPerSm) r.ctas_per_sm = 1;
         return r;
@@ -693,9 +733,8 @@ int launch_bwd(const void* dy, const void* h, const void* w, const float* rstd, 
             const int64_t budget = (t.ctas_per_sm >= 2 ? 100 : 200) * 1024;
             int64_t stages = budget / stage_bytes;
             if (stages > 8) stages = 8;
-            int64_t cthreads = (nvec + vpl - 1) / vpl;
-            cthreads = (cthreads + 31) / 32 * 32;
-            if (stages < 2 || cthreads > 512 / vpl || cthreads < 32) return;
+            const int64_t cthreads = nvec / vpl;
+            if (nvec % (32 * vpl) != 0 || stages < 2 || cthreads > 512 / vpl || cthreads < 32) return;
             const size_t smem = ((2 * stages * 8 + 2 * kr * 32 * 4 + 127) / 128) * 128 + stages * stage_bytes;
             cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
             if (e != cudaSuccess) {
@@ -705,25 +744,23 @@ int launch_bwd(const void* dy, const void* h, const void* w, const float* rstd, 
             const int64_t groups = (rows + kr - 1) / kr;
             const int64_t cap = static_cast<int64_t>(sm_count()) * t.ctas_per_sm;
             grid = static_cast<int>(groups < cap ? groups : cap);
-            kernel<<<grid, static_cast<int>(cthreads) + kProducerThreads, smem, st>>>(
+            // 1/hidden is exact in fp32 iff hidden is a power of two; then x * (1/hidden) == x / hidden bit for bit.
+            const float inv_exact = (hidden & (hidden - 1)) == 0 ? 1.0f / static_cast<float>(hidden) : 0.f;
+            kernel<<<grid, static_cast<int>(cthreads), smem, st>>>(
                 static_cast<const T*>(dy), static_cast<const T*>(h), static_cast<const T*>(w), rstd, static_cast<const T*>(dh_in),
                 static_cast<T*>(dx), static_cast<float*>(scratch), rows, static_cast<int>(nvec), static_cast<float>(hidden),
-                static_cast<int>(stages));
+                inv_exact, static_cast<int>(stages));
             rc = launch_status();
         };
         if (t.enabled) {
             if (t.vpl == 1 && t.rows == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 1, 1, kHasW, kHasDhIn>, 1, 1);
             else if (t.vpl == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 1, 2, kHasW, kHasDhIn>, 1, 2);
             else if (t.vpl == 2 && t.rows == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 2, 1, kHasW, kHasDhIn>, 2, 1);
-            else if (t.vpl == 2) try_tma(rmsnorm_bwd_tma_kernel<T, 2, 2, kHasW, kHasDhIn>, 2, 2);
-            else if (t.rows == 1) try_tma(rmsnorm_bwd_tma_kernel<T, 4, 1, kHasW, kHasDhIn>, 4, 1);
-            else try_tma(rmsnorm_bwd_tma_kernel<T, 4, 2, kHasW, kHasDhIn>, 4, 2);
+            else try_tma(rmsnorm_bwd_tma_kernel<T, 2, 2, kHasW, kHasDhIn>, 2, 2);
         }
         if (rc != -1000) {
             if (rc != 0 || !kHasW) return rc;
-            rmsnorm_dw_reduce_kernel<T><<<static_cast<int>((hidden + 31) / 32), 256, 0, st>>>(
-                static_cast<const float*>(scratch), static_cast<T*>(dw), grid, hidden);
-            return launch_status();
+            return launch_dw_reduce<T>(scratch, dw, grid, hidden, st);
         }
     }
     auto go = [&](auto kernel) {
@@ -741,9 +778,7 @@ int launch_bwd(const void* dy, const void* h, const void* w, const float* rstd, 
         default: rc = go(rmsnorm_bwd_kernel<T, 8, 1, kHasW, kHasDhIn>); break;
     }
     if (rc != 0 || !kHasW) return rc;
-    rmsnorm_dw_reduce_kernel<T><<<static_cast<int>((hidden + 31) / 32), 256, 0, st>>>(
-        static_cast<const float*>(scratch), static_cast<T*>(dw), grid, hidden);
-    return launch_status();
+    return launch_dw_reduce<T>(scratch, dw, grid, hidden, st);
 }
 
 template <typename T>
