@@ -46,118 +46,322 @@ UNIT = "GB/s"
 
 
 # --------------------------------------------------------------------------------------------------
-# Workloads
+# Workloads: one fused region pair (forward + backward) each.  Algorithmic bytes follow SURVEY §8(d):
+# every region input and output tensor counted once.
 # --------------------------------------------------------------------------------------------------
-class RmsnormResidual:
-    """BASELINE.json configs[1]; algorithmic bytes from SURVEY §8(d) row 2."""
+def _nbytes(*ts):
+    return sum(t.numel() * t.element_size() for t in ts if t is not None)
 
-    name = "rmsnorm_residual_fwd_bwd"
-    rows, hidden, eps = 8192, 4096, 1e-5
+
+class Workload:
+    """Subclasses define make(gen, device) -> dict of inputs (incl. cotangents), fwd(s) -> dict, bwd(s, f) -> dict,
+    and the CPU legs.  `sets` are NSETS independent input sets the timed loop rotates through."""
+
     dtype = torch.bfloat16
-    launches_per_step = 3  # rmsnorm_fwd_kernel, rmsnorm_bwd_kernel, rmsnorm_dw_reduce_kernel
-
-    def __init__(self):
-        e = 2
-        t = self.rows * self.hidden * e
-        self.fwd_bytes = 4 * t + self.hidden * e + self.rows * 4  # read x, r, w; write h, y, rstd
-        self.bwd_bytes = 4 * t + self.hidden * e + self.rows * 4 + self.hidden * e  # read dy, h, dh_in, w, rstd; write dx, dw
-        self.bytes_per_step = self.fwd_bytes + self.bwd_bytes
-        self.h2d_bytes = 4 * t + self.hidden * e  # x, r, dy, dh_in, w
-        self.d2h_bytes = 3 * t + self.rows * 4 + self.hidden * e  # h, y, dx, rstd, dw
-
-    def describe(self):
-        return f"{self.name} bf16 [{self.rows} tokens x {self.hidden} hidden] per GPU"
+    launches_per_step = 2
 
     def host_inputs(self, seed, pin):
-        g = torch.Generator().manual_seed(seed)
-        mk = lambda *s: torch.randn(*s, generator=g).to(self.dtype)
-        ts = dict(x=mk(self.rows, self.hidden), r=mk(self.rows, self.hidden), w=mk(self.hidden),
-                  dy=mk(self.rows, self.hidden), dh=mk(self.rows, self.hidden))
+        ts = self.make(torch.Generator().manual_seed(seed), torch.device("cpu"))
         return {k: (v.pin_memory() if pin else v) for k, v in ts.items()}
 
+    def set_bytes(self, inputs):
+        """Algorithmic bytes per step from one input set and the analytic output sizes (out_nbytes)."""
+        fo, bo = self.out_nbytes()
+        saved = self.saved_nbytes()
+        self.fwd_bytes = _nbytes(*[inputs[k] for k in self.fwd_inputs]) + fo
+        self.bwd_bytes = _nbytes(*[inputs[k] for k in self.bwd_inputs]) + saved + bo
+        self.bytes_per_step = self.fwd_bytes + self.bwd_bytes
+        self.h2d_bytes = _nbytes(*inputs.values())
+        self.d2h_bytes = fo + bo
+
+    def saved_nbytes(self):
+        return 0
+
     def alloc(self, device):
-        self.sets = []
-        for s in range(NSETS):
-            g = torch.Generator(device=device).manual_seed(1234 + s)
-            mk = lambda *sh: torch.randn(*sh, generator=g, device=device, dtype=torch.float32).to(self.dtype)
-            self.sets.append(dict(x=mk(self.rows, self.hidden), r=mk(self.rows, self.hidden), w=mk(self.hidden),
-                                  dy=mk(self.rows, self.hidden), dh=mk(self.rows, self.hidden)))
-        # saved-for-backward of each set, produced once, so the bwd-only kernel loop has its inputs
-        from b200ex import ops
-
-        for s in self.sets:
-            s["h"], _, s["rstd"] = ops.rmsnorm_fwd(s["x"], s["r"], s["w"], self.eps)
-
-    def fwd(self, i):
-        from b200ex import ops
-
-        s = self.sets[i % NSETS]
-        return ops.rmsnorm_fwd(s["x"], s["r"], s["w"], self.eps)
-
-    def bwd(self, i):
-        from b200ex import ops
-
-        s = self.sets[i % NSETS]
-        return ops.rmsnorm_bwd(s["dy"], s["h"], s["w"], s["rstd"], s["dh"])
+        self.sets = [self.make(torch.Generator(device=device).manual_seed(1234 + s), device) for s in range(NSETS)]
+        self.saved = [self.fwd(s) for s in self.sets]
+        self.set_bytes(self.sets[0])
+        f, b = self.saved[0], self.bwd(self.sets[0], self.saved[0])
+        assert _nbytes(*f.values()) + _nbytes(*b.values()) == self.d2h_bytes, "out_nbytes() disagrees with the launcher outputs"
 
     def step(self, i):
-        from b200ex import ops
-
         s = self.sets[i % NSETS]
-        h, y, rstd = ops.rmsnorm_fwd(s["x"], s["r"], s["w"], self.eps)
-        return ops.rmsnorm_bwd(s["dy"], h, s["w"], rstd, s["dh"])
+        return self.bwd(s, self.fwd(s))
 
     def kernels(self):
-        return [("rmsnorm_fwd_kernel", self.fwd, self.fwd_bytes), ("rmsnorm_bwd_kernel(+dw_reduce)", self.bwd, self.bwd_bytes)]
-
-    def e2e_step(self, host, device, out_host):
-        from b200ex import ops
-
-        d = {k: v.to(device, non_blocking=True) for k, v in host.items()}
-        h, y, rstd = ops.rmsnorm_fwd(d["x"], d["r"], d["w"], self.eps)
-        dx, dw = ops.rmsnorm_bwd(d["dy"], h, d["w"], rstd, d["dh"])
-        for k, v in (("h", h), ("y", y), ("rstd", rstd), ("dx", dx), ("dw", dw)):
-            out_host[k].copy_(v, non_blocking=True)
+        return [(self.name + " fwd", lambda i: self.fwd(self.sets[i % NSETS]), self.fwd_bytes),
+                (self.name + " bwd", lambda i: self.bwd(self.sets[i % NSETS], self.saved[i % NSETS]), self.bwd_bytes)]
 
     def e2e_out_host(self):
-        bf, f32 = self.dtype, torch.float32
-        return dict(h=torch.empty(self.rows, self.hidden, dtype=bf).pin_memory(), y=torch.empty(self.rows, self.hidden, dtype=bf).pin_memory(),
-                    rstd=torch.empty(self.rows, 1, dtype=f32).pin_memory(), dx=torch.empty(self.rows, self.hidden, dtype=bf).pin_memory(),
-                    dw=torch.empty(self.hidden, dtype=bf).pin_memory())
+        f = self.saved[0]
+        b = self.bwd(self.sets[0], f)
+        return {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in {**f, **b}.items()}
 
-    # ---- CPU legs -------------------------------------------------------------------------------
+    def e2e_step(self, host, device, out_host):
+        d = {k: v.to(device, non_blocking=True) for k, v in host.items()}
+        f = self.fwd(d)
+        b = self.bwd(d, f)
+        for k, v in {**f, **b}.items():
+            out_host[k].copy_(v, non_blocking=True)
+
     def cpu_step_port(self):
-        from oracle import regions as O
-
         hi = self.host_inputs(0, pin=False)
+        self.set_bytes(hi)
+        return lambda: self.oracle(hi)
+
+    def cpu_step_reference(self, thunder):
+        hi = self.host_inputs(0, pin=False)
+        self.set_bytes(hi)
+        fn, diff, cot = self.reference_fn()
+        jf = thunder.jit(fn, executors=["torch"])
+        args = [hi[k].clone().requires_grad_(k in diff) if hi[k].is_floating_point() else hi[k] for k in self.fwd_inputs]
+        dargs = [a for a, k in zip(args, self.fwd_inputs) if k in diff]
 
         def run():
-            h, y, rstd = O.rmsnorm_residual_fwd(hi["x"], hi["r"], hi["w"], self.eps)
-            return O.rmsnorm_residual_bwd(hi["dy"], hi["dh"], h, hi["w"], rstd)
+            outs = jf(*args)
+            outs = list(outs) if isinstance(outs, (tuple, list)) else [outs]
+            return torch.autograd.grad(outs, dargs, grad_outputs=[hi[k] for k in cot])
 
         return run
 
-    def cpu_step_reference(self, thunder):
+
+def _randn(gen, device, *shape, dtype=torch.bfloat16, scale=1.0):
+    return (torch.randn(*shape, generator=gen, device=device, dtype=torch.float32) * scale).to(dtype)
+
+
+class RmsnormResidual(Workload):
+    """BASELINE.json configs[1]: fwd reads x, r, w and writes h, y, rstd (268 476 416 B); bwd reads dy, h, dh_in, w, rstd
+    and writes dx (= dr, written once) and dw (268 484 608 B)."""
+
+    name = "rmsnorm_residual"
+    rows, hidden, eps = 8192, 4096, 1e-5
+    launches_per_step = 3  # rmsnorm_fwd_kernel, rmsnorm_bwd_tma_kernel, colsum_finalize_kernel
+    fwd_inputs, bwd_inputs, bwd_saved = ("x", "r", "w"), ("dy", "dh", "w"), ("h", "rstd")
+
+    def describe(self):
+        return f"{self.name}_fwd_bwd bf16 [{self.rows} tokens x {self.hidden} hidden] per GPU"
+
+    def out_nbytes(self):
+        t = self.rows * self.hidden * 2
+        return 2 * t + self.rows * 4, t + self.hidden * 2  # (h, y, rstd), (dx, dw)
+
+    def saved_nbytes(self):
+        return self.rows * self.hidden * 2 + self.rows * 4  # h, rstd
+
+    def make(self, g, dev):
+        R, H = self.rows, self.hidden
+        return dict(x=_randn(g, dev, R, H), r=_randn(g, dev, R, H), w=_randn(g, dev, H), dy=_randn(g, dev, R, H), dh=_randn(g, dev, R, H))
+
+    def fwd(self, s):
+        from b200ex import ops
+
+        h, y, rstd = ops.rmsnorm_fwd(s["x"], s["r"], s["w"], self.eps)
+        return dict(h=h, y=y, rstd=rstd)
+
+    def bwd(self, s, f):
+        from b200ex import ops
+
+        dx, dw = ops.rmsnorm_bwd(s["dy"], f["h"], s["w"], f["rstd"], s["dh"])
+        return dict(dx=dx, dw=dw)
+
+    def oracle(self, hi):
+        from oracle import regions as O
+
+        h, y, rstd = O.rmsnorm_residual_fwd(hi["x"], hi["r"], hi["w"], self.eps)
+        return O.rmsnorm_residual_bwd(hi["dy"], hi["dh"], h, hi["w"], rstd)
+
+    def reference_fn(self):
         import torch.nn.functional as F
 
-        hi = self.host_inputs(0, pin=False)
         hidden, eps = self.hidden, self.eps
 
         def fn(x, r, w):
             h = x + r
             return h, F.rms_norm(h, (hidden,), w, eps)
 
-        jf = thunder.jit(fn, executors=["torch"])
-        x, r, w = (hi[k].clone().requires_grad_(True) for k in ("x", "r", "w"))
-
-        def run():
-            h, y = jf(x, r, w)
-            return torch.autograd.grad([h, y], [x, r, w], grad_outputs=[hi["dh"], hi["dy"]])
-
-        return run
+        return fn, ("x", "r", "w"), ("dh", "dy")
 
 
-WORKLOADS = {"rmsnorm": RmsnormResidual}
+class Swiglu(Workload):
+    """Llama-3-8B MLP activation (configs[2] region): fwd 3 x 234 881 024 B, bwd 5 x 234 881 024 B."""
+
+    name = "swiglu"
+    rows, inter = 8192, 14336
+    fwd_inputs, bwd_inputs, bwd_saved = ("a", "b"), ("a", "b", "g"), ()
+
+    def describe(self):
+        return f"swiglu_fwd_bwd bf16 [{self.rows} tokens x {self.inter}] per GPU"
+
+    def out_nbytes(self):
+        t = self.rows * self.inter * 2
+        return t, 2 * t
+
+    def make(self, g, dev):
+        return dict(a=_randn(g, dev, self.rows, self.inter), b=_randn(g, dev, self.rows, self.inter), g=_randn(g, dev, self.rows, self.inter))
+
+    def fwd(self, s):
+        from b200ex import ops
+
+        return dict(out=ops.swiglu_fwd(s["a"], s["b"]))
+
+    def bwd(self, s, f):
+        from b200ex import ops
+
+        da, db = ops.swiglu_bwd(s["a"], s["b"], s["g"])
+        return dict(da=da, db=db)
+
+    def oracle(self, hi):
+        from oracle import regions as O
+
+        return O.swiglu_fwd(hi["a"], hi["b"]), O.swiglu_bwd(hi["a"], hi["b"], hi["g"])
+
+    def reference_fn(self):
+        import torch.nn.functional as F
+
+        return (lambda a, b: F.silu(a) * b), ("a", "b"), ("g",)
+
+
+class CrossEntropy(Workload):
+    """BASELINE.json configs[3]: bf16 logits [8192, 128256]; fwd reads logits once (2.10 GB), bwd reads logits and
+    writes dlogits (4.20 GB)."""
+
+    name = "cross_entropy"
+    rows, vocab = 8192, 128256
+    launches_per_step = 3  # ce_fwd_kernel, ce_finalize_kernel, ce_bwd_kernel
+    fwd_inputs, bwd_inputs, bwd_saved = ("logits", "target"), ("logits", "target", "g"), ("row_max", "row_logsum", "n_valid")
+
+    def describe(self):
+        return f"cross_entropy_fwd_bwd bf16 logits [{self.rows} tokens x {self.vocab} vocab] per GPU"
+
+    def out_nbytes(self):
+        return 2 + 2 * self.rows * 4 + 8, self.rows * self.vocab * 2  # (loss, row_max, row_logsum, n_valid), dlogits
+
+    def saved_nbytes(self):
+        return 2 * self.rows * 4 + 8
+
+    def make(self, g, dev):
+        t = torch.randint(0, self.vocab, (self.rows,), generator=g, device=dev)
+        t[::113] = -100
+        return dict(logits=_randn(g, dev, self.rows, self.vocab), target=t, g=torch.ones((), dtype=self.dtype, device=dev))
+
+    def fwd(self, s):
+        from b200ex import ops
+
+        loss, rmax, rls, nv = ops.cross_entropy_fwd(s["logits"], s["target"], -100)
+        return dict(loss=loss, row_max=rmax, row_logsum=rls, n_valid=nv)
+
+    def bwd(self, s, f):
+        from b200ex import ops
+
+        return dict(dlogits=ops.cross_entropy_bwd(s["g"], s["logits"], s["target"], f["row_max"], f["row_logsum"], f["n_valid"], -100))
+
+    def oracle(self, hi):
+        from oracle import regions as O
+
+        loss, logp, nv = O.cross_entropy_fwd(hi["logits"], hi["target"], -100)
+        return O.cross_entropy_bwd(hi["g"], logp, hi["target"], nv, -100)
+
+    def reference_fn(self):
+        import torch.nn.functional as F
+
+        return (lambda logits, target: F.cross_entropy(logits, target, ignore_index=-100)), ("logits",), ("g",)
+
+
+class QkvRope(Workload):
+    """Llama-3-8B attention slice (configs[2] region): qkv [2, 4096, 6144] -> q, k, v [2, 32, 4096, 128] (k, v
+    materialised at 32 heads as the reference's expand+reshape does: 304 MB forward)."""
+
+    name = "qkv_rope"
+    B, T, n_head, groups, hs = 2, 4096, 32, 8, 128
+    fwd_inputs, bwd_inputs, bwd_saved = ("qkv", "cos", "sin"), ("dq", "dk", "dv", "cos", "sin"), ()
+
+    def describe(self):
+        return f"qkv_split_rope_fwd_bwd bf16 qkv [{self.B}, {self.T}, {(self.n_head + 2 * self.groups) * self.hs}] per GPU"
+
+    def out_nbytes(self):
+        return 3 * self.B * self.n_head * self.T * self.hs * 2, self.B * self.T * (self.n_head + 2 * self.groups) * self.hs * 2
+
+    def make(self, g, dev):
+        B, T, nh, G, hs = self.B, self.T, self.n_head, self.groups, self.hs
+        return dict(qkv=_randn(g, dev, B, T, (nh + 2 * G) * hs), cos=_randn(g, dev, T, hs), sin=_randn(g, dev, T, hs),
+                    dq=_randn(g, dev, B, nh, T, hs), dk=_randn(g, dev, B, nh, T, hs), dv=_randn(g, dev, B, nh, T, hs))
+
+    def fwd(self, s):
+        from b200ex import ops
+
+        q, k, v = ops.qkv_rope_fwd(s["qkv"], s["cos"], s["sin"], self.n_head, self.groups, self.hs, self.hs)
+        return dict(q=q, k=k, v=v)
+
+    def bwd(self, s, f):
+        from b200ex import ops
+
+        return dict(dqkv=ops.qkv_rope_bwd(s["dq"], s["dk"], s["dv"], s["cos"], s["sin"], self.n_head, self.groups, self.hs, self.hs))
+
+    def oracle(self, hi):
+        from oracle import regions as O
+
+        a = (self.n_head, self.groups, self.hs, self.hs)
+        return O.qkv_split_rope_fwd(hi["qkv"], hi["cos"], hi["sin"], *a), O.qkv_split_rope_bwd(hi["dq"], hi["dk"], hi["dv"], hi["cos"], hi["sin"], *a)
+
+    def reference_fn(self):
+        B, T, nh, G, hs = self.B, self.T, self.n_head, self.groups, self.hs
+
+        def apply_rope(x, cos, sin):
+            x1, x2 = x[..., : hs // 2], x[..., hs // 2 :]
+            return ((x * cos) + (torch.cat((-x2, x1), dim=-1) * sin)).to(dtype=x.dtype)
+
+        def fn(qkv, cos, sin):
+            qpk = nh // G
+            t = qkv.view(B, T, G, qpk + 2, hs).permute(0, 2, 3, 1, 4)
+            q, k, v = t.split((qpk, 1, 1), dim=2)
+            k, v = k.expand(B, G, qpk, T, hs), v.expand(B, G, qpk, T, hs)
+            q, k, v = q.reshape(B, -1, T, hs), k.reshape(B, -1, T, hs), v.reshape(B, -1, T, hs)
+            return apply_rope(q, cos, sin), apply_rope(k, cos, sin), v
+
+        return fn, ("qkv",), ("dq", "dk", "dv")
+
+
+class BiasGelu(Workload):
+    """bias + GELU on a GPT-2-XL-like MLP activation: bf16 [8192 tokens, 6400]."""
+
+    name = "bias_gelu"
+    rows, hidden = 8192, 6400
+    launches_per_step = 3
+    fwd_inputs, bwd_inputs, bwd_saved = ("x", "b"), ("x", "b", "g"), ()
+
+    def describe(self):
+        return f"bias_gelu_fwd_bwd bf16 [{self.rows} tokens x {self.hidden}] per GPU"
+
+    def out_nbytes(self):
+        t = self.rows * self.hidden * 2
+        return t, t + self.hidden * 2
+
+    def make(self, g, dev):
+        return dict(x=_randn(g, dev, self.rows, self.hidden), b=_randn(g, dev, self.hidden), g=_randn(g, dev, self.rows, self.hidden))
+
+    def fwd(self, s):
+        from b200ex import ops
+
+        return dict(out=ops.bias_act_fwd(s["x"], s["b"], "gelu"))
+
+    def bwd(self, s, f):
+        from b200ex import ops
+
+        dx, db = ops.bias_act_bwd(s["x"], s["b"], s["g"], "gelu")
+        return dict(dx=dx, db=db)
+
+    def oracle(self, hi):
+        from oracle import regions as O
+
+        return O.bias_gelu_fwd(hi["x"], hi["b"]), O.bias_gelu_bwd(hi["x"], hi["b"], hi["g"])
+
+    def reference_fn(self):
+        import torch.nn.functional as F
+
+        return (lambda x, b: F.gelu(x + b)), ("x", "b"), ("g",)
+
+
+WORKLOADS = {"rmsnorm": RmsnormResidual, "swiglu": Swiglu, "cross_entropy": CrossEntropy, "qkv_rope": QkvRope, "bias_gelu": BiasGelu}
 
 
 # --------------------------------------------------------------------------------------------------
@@ -281,7 +485,7 @@ def run_reference_arm(args, wl):
     torch.set_num_threads(os.cpu_count() or 1)
     thunder = import_reference()
     kind = "reference" if thunder is not None else "port"
-    run = wl.cpu_step_reference(thunder) if thunder is not None else wl.cpu_step_port()
+    run = wl.cpu_step_reference(thunder) if thunder is not None else wl.cpu_step_port()  # also sets wl.bytes_per_step
     for _ in range(max(1, args.warmup)):
         run()
     t0 = time.perf_counter()
@@ -402,7 +606,7 @@ def main():
         e2e = {"value": world * wl.bytes_per_step * e2e_steps / (ems.item() / 1e3) / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes,
                "ms_per_step": ems.item() / e2e_steps, "steps": e2e_steps,
-               "api": "b200ex.ops.rmsnorm_fwd/rmsnorm_bwd on pinned host tensors (H2D + launch + D2H per step)"}
+               "api": "b200ex.ops launchers on pinned host tensors (H2D + launch + D2H per step)"}
 
     sampler.mark_load(False)
     clocks = sampler.stop() if rank == 0 else None
@@ -416,7 +620,7 @@ def main():
             "metric": METRIC, "value": world * wl.bytes_per_step * args.steps / (total_ms / 1e3) / 1e9, "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": wl.describe(), "l2": f"inputs larger than L2: rotating {NSETS} buffer sets (1.07 GB working set)",
+            "config": {"workload": wl.describe(), "l2": f"inputs larger than L2: rotating {NSETS} buffer sets ({NSETS * wl.h2d_bytes / 1e9:.2f} GB of inputs)",
                        "sharding": "each rank runs the region on its own micro-batch; no data-path collective"},
             "roofline": {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbps"], "peak": peak, "unit": UNIT,
                          "frac": dom["achieved_gbps"] / peak, "frac_of_nominal_8TBps": dom["achieved_gbps"] / 8000.0,

@@ -85,6 +85,94 @@ B200K_API int b200k_rmsnorm_bwd(const void* dy, const void* h, const void* weigh
                       void* scratch, int64_t scratch_bytes,
                       int64_t rows, int64_t hidden, int dtype, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * SwiGLU forward — SURVEY §8 row a7.  Replaces the region `silu(a) * b` built from ltorch.silu
+ * (thunder/torch/__init__.py:2266 -> thunder/clang/__init__.py:1417) + ltorch.mul.
+ *   u = round_T(a / (1 + exp(-a)));  out = round_T(f32(u) * f32(b))
+ * a, b, out: n contiguous elements of `dtype`.
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_swiglu_fwd(const void* a, const void* b, void* out, int64_t n, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * SwiGLU backward — SURVEY §8 row a8 (autodiff of a7; silu recomputed in the region by
+ * thunder/core/rematerialization.py:407).  g is the cotangent of out.
+ *   db = round_T(u * g);  gu = round_T(b * g)
+ *   s  = round_T(1 / round_T(1 + round_T(exp(-a))))
+ *   da = round_T(round_T(gu * s) * round_T(1 + round_T(a * round_T(1 - s))))
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_swiglu_bwd(const void* a, const void* b, const void* g, void* da, void* db, int64_t n, int dtype,
+                               void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Softmax cross-entropy forward — SURVEY §8 row a12.  Replaces ltorch.cross_entropy
+ * (thunder/torch/__init__.py:5226-5270; log_softmax :5839-5851 + nll_loss :6018-6031), the op the
+ * reference claims in thunder/executors/nvfuserex_impl.py:2967-3018.
+ * logits [rows, vocab] of `dtype` row-major; target int64 [rows]; reduction 1 = mean, 2 = sum.
+ * Per row (streamed once, online softmax): row_max = max_j x, row_logsum = log sum_j exp(x - max),
+ * row_nll = -round_T((x[target] - max) - logsum), or 0 when target == ignore_index.
+ * loss (one element of `dtype`, may be NULL to skip) = round_T(round_T(sum row_nll) / n_valid) for mean,
+ * round_T(sum row_nll) for sum; n_valid (int64, may be NULL) = #rows with target != ignore_index.
+ * row_max, row_logsum, row_nll: fp32 [rows] outputs (the first two are what backward needs).
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_cross_entropy_fwd(const void* logits, const int64_t* target, float* row_max, float* row_logsum,
+                                      float* row_nll, void* loss, int64_t* n_valid, int64_t rows, int64_t vocab,
+                                      int64_t ignore_index, int reduction, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Softmax cross-entropy backward — SURVEY §8 row a13.  Replaces nll_loss_backward
+ * (thunder/torch/__init__.py:6035-6047, thunder/executors/torchex.py:1731-1783) + log_softmax_backward
+ * (:5859-5864); the reference's fused variant is nvfuserex_impl.py:3043-3094.
+ *   d = -round_T(g / round_T(n_valid))  (mean)   or  -g  (sum);   logp = round_T((x - max) - logsum)
+ *   dlogits[i, j] = round_T([j == target_i] * d - exp(logp) * d)   for valid rows, 0 for ignored rows
+ * g: one element of `dtype` (device pointer); n_valid: the int64 the forward wrote (mean only).
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_cross_entropy_bwd(const void* g, const void* logits, const int64_t* target, const float* row_max,
+                                      const float* row_logsum, const int64_t* n_valid, void* dlogits, int64_t rows,
+                                      int64_t vocab, int64_t ignore_index, int reduction, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * QKV split + RoPE (+ GQA expand) forward — SURVEY §8 row a9.  Replaces the region traced from
+ * thunder/benchmarks/__init__.py:2282-2328 (vendored LitGPT attention slice; litgpt apply_rope),
+ * which the reference routes to a fusion executor (thunder/executors/torch_compile.py:198-234).
+ * qkv [B, T, G, q_per_kv + 2, hs] contiguous; cos, sin [T, rope_n_elem];
+ * q [B, G*q_per_kv, T, hs]; k, v [B, Hkv, T, hs] with Hkv = G*q_per_kv if expand_kv else G.
+ * For q and k heads, over the first rope_n_elem features (half = rope_n_elem / 2):
+ *   out[j] = round_T(round_T(x[j] * cos[j]) + round_T(rot[j] * sin[j])),  rot = cat(-x[half:], x[:half])
+ * the remaining features and all of v are copied.
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_qkv_rope_fwd(const void* qkv, const void* cos, const void* sin, void* q, void* k, void* v,
+                                 int64_t B, int64_t T, int n_query_groups, int q_per_kv, int head_size, int rope_n_elem,
+                                 int expand_kv, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * QKV split + RoPE backward — SURVEY §8 row a10 (slice vjp = pad, cat vjp = slice, expand vjp = sum
+ * over q_per_kv in fp32 rounded once, final cat into dqkv).  Shapes as in the forward; writes
+ * dqkv [B, T, G, q_per_kv + 2, hs].
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_qkv_rope_bwd(const void* dq, const void* dk, const void* dv, const void* cos, const void* sin,
+                                 void* dqkv, int64_t B, int64_t T, int n_query_groups, int q_per_kv, int head_size,
+                                 int rope_n_elem, int expand_kv, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * bias + activation forward — SURVEY §8 row a11.  act: 0 = none, 1 = relu (ltorch.relu ->
+ * where(a > 0, a, 0)), 2 = gelu, erf form (thunder/torch/__init__.py:2071-2082).
+ *   a = round_T(x + bias)  (a = x when bias == NULL);  out = act(a) with one round_T per ltorch op.
+ * x, out [rows, hidden]; bias [hidden].
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_bias_act_fwd(const void* x, const void* bias, void* out, int64_t rows, int64_t hidden, int act,
+                                 int dtype, void* stream);
+
+/* Scratch bytes b200k_bias_act_bwd needs when bias != NULL. */
+B200K_API int64_t b200k_bias_act_bwd_scratch_bytes(int64_t rows, int64_t hidden);
+
+/* ---------------------------------------------------------------------------------------------
+ * bias + activation backward — SURVEY §8 row a11.  dx = act'(a) applied to g with the reference's
+ * rounding points; dbias = round_T(sum_rows f32(dx)) (not written when bias == NULL).
+ * scratch as for b200k_rmsnorm_bwd (contents ignored on entry, unspecified on exit).
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_bias_act_bwd(const void* x, const void* bias, const void* g, void* dx, void* dbias, void* scratch,
+                                 int64_t scratch_bytes, int64_t rows, int64_t hidden, int act, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,10 @@ import torch
 
 from . import _lib
 
-__all__ = ["rmsnorm_fwd", "rmsnorm_bwd", "DTYPE_CODE"]
+__all__ = [
+    "rmsnorm_fwd", "rmsnorm_bwd", "swiglu_fwd", "swiglu_bwd", "cross_entropy_fwd", "cross_entropy_bwd",
+    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "ACT_CODE", "DTYPE_CODE",
+]
 
 DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
 
@@ -95,3 +98,146 @@ def rmsnorm_bwd(dy, h, weight, rstd, dh_in=None):
         )
     _lib.check(rc, "b200k_rmsnorm_bwd")
     return dx.view(shape), dw
+
+
+def _contig(t):
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def swiglu_fwd(a, b):
+    """silu(a) * b — see b200k_swiglu_fwd."""
+    dev = _require_cuda(a, b)
+    a, b = _contig(a), _contig(b)
+    out = torch.empty_like(a)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().b200k_swiglu_fwd(_ptr(a), _ptr(b), _ptr(out), a.numel(), _code(a), _stream(dev))
+    _lib.check(rc, "b200k_swiglu_fwd")
+    return out
+
+
+def swiglu_bwd(a, b, g):
+    """(da, db) for out = silu(a) * b — see b200k_swiglu_bwd."""
+    dev = _require_cuda(a, b, g)
+    a, b, g = _contig(a), _contig(b), _contig(g)
+    da, db = torch.empty_like(a), torch.empty_like(a)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().b200k_swiglu_bwd(_ptr(a), _ptr(b), _ptr(g), _ptr(da), _ptr(db), a.numel(), _code(a), _stream(dev))
+    _lib.check(rc, "b200k_swiglu_bwd")
+    return da, db
+
+
+REDUCTION_CODE = {"mean": 1, "sum": 2}
+
+
+def cross_entropy_fwd(logits, target, ignore_index: int = -100, reduction: str = "mean"):
+    """(loss, row_max, row_logsum, n_valid) — see b200k_cross_entropy_fwd.  logits [rows, vocab], target int64 [rows]."""
+    dev = _require_cuda(logits, target)
+    if logits.dim() != 2 or target.dim() != 1 or target.dtype != torch.int64 or target.shape[0] != logits.shape[0]:
+        raise ValueError("b200ex.cross_entropy_fwd: expected logits [rows, vocab] and int64 target [rows]")
+    logits, target = _contig(logits), _contig(target)
+    rows, vocab = logits.shape
+    f32 = dict(dtype=torch.float32, device=dev)
+    row_max, row_logsum, row_nll = torch.empty(rows, **f32), torch.empty(rows, **f32), torch.empty(rows, **f32)
+    loss = torch.empty((), dtype=logits.dtype, device=dev)
+    n_valid = torch.empty((), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().b200k_cross_entropy_fwd(
+            _ptr(logits), _ptr(target), _ptr(row_max), _ptr(row_logsum), _ptr(row_nll), _ptr(loss), _ptr(n_valid),
+            rows, vocab, int(ignore_index), REDUCTION_CODE[reduction], _code(logits), _stream(dev),
+        )
+    _lib.check(rc, "b200k_cross_entropy_fwd")
+    return loss, row_max, row_logsum, n_valid
+
+
+def cross_entropy_bwd(g, logits, target, row_max, row_logsum, n_valid, ignore_index: int = -100, reduction: str = "mean"):
+    """dlogits — see b200k_cross_entropy_bwd.  g is the 0-dim cotangent of the loss."""
+    dev = _require_cuda(g, logits, target, row_max, row_logsum, n_valid)
+    logits, target = _contig(logits), _contig(target)
+    rows, vocab = logits.shape
+    g = g.to(logits.dtype) if g.dtype != logits.dtype else g
+    dlogits = torch.empty_like(logits)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().b200k_cross_entropy_bwd(
+            _ptr(g), _ptr(logits), _ptr(target), _ptr(row_max), _ptr(row_logsum), _ptr(n_valid), _ptr(dlogits),
+            rows, vocab, int(ignore_index), REDUCTION_CODE[reduction], _code(logits), _stream(dev),
+        )
+    _lib.check(rc, "b200k_cross_entropy_bwd")
+    return dlogits
+
+
+def _expand_kv(n_head: int, n_query_groups: int) -> bool:
+    return n_query_groups != n_head and n_query_groups != 1
+
+
+def qkv_rope_fwd(qkv, cos, sin, n_head: int, n_query_groups: int, head_size: int, rope_n_elem: int):
+    """(q, k, v) from the fused qkv projection — see b200k_qkv_rope_fwd."""
+    dev = _require_cuda(qkv, cos, sin)
+    qkv, cos, sin = _contig(qkv), _contig(cos), _contig(sin)
+    B, T, _ = qkv.shape
+    qpk = n_head // n_query_groups
+    expand = _expand_kv(n_head, n_query_groups)
+    hkv = n_head if expand else n_query_groups
+    q = torch.empty(B, n_head, T, head_size, dtype=qkv.dtype, device=dev)
+    k = torch.empty(B, hkv, T, head_size, dtype=qkv.dtype, device=dev)
+    v = torch.empty(B, hkv, T, head_size, dtype=qkv.dtype, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().b200k_qkv_rope_fwd(
+            _ptr(qkv), _ptr(cos), _ptr(sin), _ptr(q), _ptr(k), _ptr(v), B, T, n_query_groups, qpk, head_size, rope_n_elem,
+            int(expand), _code(qkv), _stream(dev),
+        )
+    _lib.check(rc, "b200k_qkv_rope_fwd")
+    return q, k, v
+
+
+def qkv_rope_bwd(dq, dk, dv, cos, sin, n_head: int, n_query_groups: int, head_size: int, rope_n_elem: int):
+    """dqkv [B, T, (n_head + 2 * n_query_groups) * head_size] — see b200k_qkv_rope_bwd."""
+    dev = _require_cuda(dq, dk, dv, cos, sin)
+    dq, dk, dv, cos, sin = _contig(dq), _contig(dk), _contig(dv), _contig(cos), _contig(sin)
+    B, _, T, _ = dq.shape
+    qpk = n_head // n_query_groups
+    expand = _expand_kv(n_head, n_query_groups)
+    dqkv = torch.empty(B, T, (n_head + 2 * n_query_groups) * head_size, dtype=dq.dtype, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().b200k_qkv_rope_bwd(
+            _ptr(dq), _ptr(dk), _ptr(dv), _ptr(cos), _ptr(sin), _ptr(dqkv), B, T, n_query_groups, qpk, head_size, rope_n_elem,
+            int(expand), _code(dq), _stream(dev),
+        )
+    _lib.check(rc, "b200k_qkv_rope_bwd")
+    return dqkv
+
+
+ACT_CODE = {"none": 0, "relu": 1, "gelu": 2}
+
+
+def bias_act_fwd(x, bias, act: str):
+    """act(x + bias) — see b200k_bias_act_fwd."""
+    dev = _require_cuda(x, bias)
+    shape = x.shape
+    x2 = _rows2d(x)
+    b = _contig(bias) if bias is not None else None
+    out = torch.empty_like(x2)
+    rows, hidden = x2.shape
+    with torch.cuda.device(dev):
+        rc = _lib.lib().b200k_bias_act_fwd(_ptr(x2), _ptr(b), _ptr(out), rows, hidden, ACT_CODE[act], _code(x), _stream(dev))
+    _lib.check(rc, "b200k_bias_act_fwd")
+    return out.view(shape)
+
+
+def bias_act_bwd(x, bias, g, act: str):
+    """(dx, dbias) — see b200k_bias_act_bwd.  dbias is None when bias is None."""
+    dev = _require_cuda(x, bias, g)
+    shape = x.shape
+    x2, g2 = _rows2d(x), _rows2d(g)
+    b = _contig(bias) if bias is not None else None
+    rows, hidden = x2.shape
+    dx = torch.empty_like(x2)
+    db = torch.empty_like(b) if b is not None else None
+    L = _lib.lib()
+    with torch.cuda.device(dev):
+        nbytes = L.b200k_bias_act_bwd_scratch_bytes(rows, hidden) if b is not None else 0
+        scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev) if b is not None else None
+        rc = L.b200k_bias_act_bwd(
+            _ptr(x2), _ptr(b), _ptr(g2), _ptr(dx), _ptr(db), _ptr(scratch), nbytes, rows, hidden, ACT_CODE[act], _code(x), _stream(dev)
+        )
+    _lib.check(rc, "b200k_bias_act_bwd")
+    return dx.view(shape), db

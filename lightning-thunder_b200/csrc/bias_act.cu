@@ -1,0 +1,276 @@
+// bias + activation forward / backward.
+//
+// x, g, out, dx: [rows, hidden] row-major; bias, dbias: [hidden].  Thread t of a CTA owns the 16-byte
+// vectors t, t + blockDim.x, ... of a column tile, the CTA strides over rows, so bias stays in
+// registers and the backward can keep fp32 partial column sums of dx per thread (dbias), written as
+// one partial row per CTA and folded by colsum_finalize (deterministic, no atomics).
+// act: 0 = none (bias add only), 1 = relu, 2 = gelu (erf form).
+#include "common.cuh"
+#include "reduce.cuh"
+
+namespace b200k {
+namespace {
+
+constexpr int kBaThreads = 256;
+constexpr int kBaVpl = 2;
+constexpr int kBaRowParts = 4;  // CTAs per SM along rows (sizes the scratch)
+constexpr float kInvSqrt2 = 0.70710678118654752440f;
+constexpr float kTwoOverSqrtPi = 1.1283791670955126f;
+
+template <typename T, int kAct>
+__device__ __forceinline__ void act_fwd(float* a /* rounded pre-activation, in/out */, int n) {
+    using V = Vec<T>;
+#pragma unroll
+    for (int e = 0; e < n; e += 2) {
+        float a0 = a[e], a1 = a[e + 1];
+        if constexpr (kAct == 1) {
+            a[e] = a0 > 0.f ? a0 : 0.f;
+            a[e + 1] = a1 > 0.f ? a1 : 0.f;
+        } else if constexpr (kAct == 2) {
+            float z0 = a0 * kInvSqrt2, z1 = a1 * kInvSqrt2;
+            V::rnd2(z0, z1);
+            float r0 = erff(z0), r1 = erff(z1);
+            V::rnd2(r0, r1);
+            r0 *= 0.5f, r1 *= 0.5f;
+            V::rnd2(r0, r1);
+            r0 += 0.5f, r1 += 0.5f;
+            V::rnd2(r0, r1);
+            a[e] = a0 * r0;
+            a[e + 1] = a1 * r1;
+        }
+    }
+}
+
+template <typename T, int kAct>
+__device__ __forceinline__ void act_bwd(const float* a, const float* g, float* dx, int n) {
+    using V = Vec<T>;
+    constexpr bool kIsF32 = V::kDtype == B200K_F32;
+#pragma unroll
+    for (int e = 0; e < n; e += 2) {
+        const float a0 = a[e], a1 = a[e + 1], g0 = g[e], g1 = g[e + 1];
+        if constexpr (kAct == 0) {
+            dx[e] = g0, dx[e + 1] = g1;
+        } else if constexpr (kAct == 1) {
+            dx[e] = a0 > 0.f ? g0 : 0.f;
+            dx[e + 1] = a1 > 0.f ? g1 : 0.f;
+        } else {
+            float z0 = a0 * kInvSqrt2, z1 = a1 * kInvSqrt2;
+            V::rnd2(z0, z1);
+            float c0 = erff(z0), c1 = erff(z1);
+            V::rnd2(c0, c1);
+            c0 *= 0.5f, c1 *= 0.5f;
+            V::rnd2(c0, c1);
+            c0 += 0.5f, c1 += 0.5f;
+            V::rnd2(c0, c1);  // cdf
+            float p0 = c0 * g0, p1 = c1 * g1;
+            V::rnd2(p0, p1);
+            float q0 = a0 * g0, q1 = a1 * g1;
+            V::rnd2(q0, q1);
+            q0 *= 0.5f, q1 *= 0.5f;
+            V::rnd2(q0, q1);
+            const float pdf0 = kTwoOverSqrtPi * expf(-(z0 * z0)), pdf1 = kTwoOverSqrtPi * expf(-(z1 * z1));
+            float r0 = pdf0 * q0, r1 = pdf1 * q1;
+            V::rnd2(r0, r1);
+            r0 *= kInvSqrt2, r1 *= kInvSqrt2;
+            if constexpr (!kIsF32) V::rnd2(r0, r1);
+            dx[e] = p0 + r0;
+            dx[e + 1] = p1 + r1;
+        }
+    }
+}
+
+// grid = (row parts, column tiles); column tile = blockDim.x * kBaVpl vectors.
+template <typename T, int kAct, bool kHasBias, bool kBwd>
+__global__ void __launch_bounds__(kBaThreads)
+bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __restrict__ g, T* __restrict__ out,
+                float* __restrict__ partial, int64_t rows, int nvec) {
+    using V = Vec<T>;
+    constexpr int kE = V::kElems;
+    const int tid = threadIdx.x;
+    const int v0 = blockIdx.y * (kBaThreads * kBaVpl) + tid;
+    float bf[kBaVpl][kE], acc[kBaVpl][kE];
+#pragma unroll
+    for (int i = 0; i < kBaVpl; ++i) {
+        const int v = v0 + i * kBaThreads;
+#pragma unroll
+        for (int e = 0; e < kE; ++e) bf[i][e] = 0.f, acc[i][e] = 0.f;
+        if (kHasBias && v < nvec) V::unpack(ld_keep(reinterpret_cast<const uint4*>(bias) + v), bf[i]);
+    }
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        uint4 xv[kBaVpl], gv[kBaVpl];
+#pragma unroll
+        for (int i = 0; i < kBaVpl; ++i) {
+            const int v = v0 + i * kBaThreads;
+            if (v < nvec) {
+                xv[i] = ld_stream(reinterpret_cast<const uint4*>(x) + row * nvec + v);
+                if constexpr (kBwd) gv[i] = ld_stream(reinterpret_cast<const uint4*>(g) + row * nvec + v);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < kBaVpl; ++i) {
+            const int v = v0 + i * kBaThreads;
+            if (v < nvec) {
+                float a[kE], o[kE];
+                V::unpack(xv[i], a);
+                if constexpr (kHasBias) {
+#pragma unroll
+                    for (int e = 0; e < kE; e += 2) {
+                        a[e] += bf[i][e];
+                        a[e + 1] += bf[i][e + 1];
+                        V::rnd2(a[e], a[e + 1]);
+                    }
+                }
+                if constexpr (kBwd) {
+                    float gf[kE];
+                    V::unpack(gv[i], gf);
+                    act_bwd<T, kAct>(a, gf, o, kE);
+                    if constexpr (kHasBias) {
+#pragma unroll
+                        for (int e = 0; e < kE; e += 2) {
+                            float d0 = o[e], d1 = o[e + 1];
+                            V::rnd2(d0, d1);
+                            acc[i][e] += d0;
+                            acc[i][e + 1] += d1;
+                        }
+                    }
+                } else {
+                    act_fwd<T, kAct>(a, kE);
+#pragma unroll
+                    for (int e = 0; e < kE; ++e) o[e] = a[e];
+                }
+                st_stream(reinterpret_cast<uint4*>(out) + row * nvec + v, V::pack(o));
+            }
+        }
+    }
+    if constexpr (kBwd && kHasBias) {
+        float* prow = partial + static_cast<int64_t>(blockIdx.x) * nvec * kE;
+#pragma unroll
+        for (int i = 0; i < kBaVpl; ++i) {
+            const int v = v0 + i * kBaThreads;
+            if (v < nvec) {
+#pragma unroll
+                for (int q = 0; q < kE / 4; ++q)
+                    reinterpret_cast<float4*>(prow + static_cast<int64_t>(v) * kE)[q] =
+                        make_float4(acc[i][4 * q], acc[i][4 * q + 1], acc[i][4 * q + 2], acc[i][4 * q + 3]);
+            }
+        }
+    }
+    if constexpr (kBwd) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
+// Scalar fallback for hidden not a multiple of the vector width / unaligned pointers: one thread per column.
+template <typename T, bool kBwd>
+__global__ void __launch_bounds__(256)
+bias_act_generic_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __restrict__ g, T* __restrict__ out,
+                        T* __restrict__ dbias, int64_t rows, int64_t hidden, int act) {
+    using V = Vec<T>;
+    const int64_t col = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (col >= hidden) return;
+    const float b = bias != nullptr ? V::load1(bias, col) : 0.f;
+    float acc = 0.f;
+    for (int64_t r = 0; r < rows; ++r) {
+        float a[2] = {V::load1(x, r * hidden + col), 0.f};
+        if (bias != nullptr) a[0] = V::rnd(a[0] + b);
+        float o[2] = {0.f, 0.f};
+        if constexpr (kBwd) {
+            const float gf[2] = {V::load1(g, r * hidden + col), 0.f};
+            if (act == 0) act_bwd<T, 0>(a, gf, o, 2);
+            else if (act == 1) act_bwd<T, 1>(a, gf, o, 2);
+            else act_bwd<T, 2>(a, gf, o, 2);
+            acc += V::rnd(o[0]);
+        } else {
+            if (act == 1) act_fwd<T, 1>(a, 2);
+            else if (act == 2) act_fwd<T, 2>(a, 2);
+            o[0] = a[0];
+        }
+        V::store1(out, r * hidden + col, o[0]);
+    }
+    if (kBwd && dbias != nullptr) V::store1(dbias, col, acc);
+}
+
+int row_parts(int64_t rows, int col_tiles) {
+    int64_t parts = static_cast<int64_t>(sm_count()) * kBaRowParts / (col_tiles > 0 ? col_tiles : 1);
+    if (parts < 1) parts = 1;
+    return static_cast<int>(rows < parts ? rows : parts);
+}
+
+template <typename T, bool kBwd>
+int run(const void* x, const void* bias, const void* g, void* out, void* dbias, void* scratch, int64_t scratch_bytes, int64_t rows,
+        int64_t hidden, int act, cudaStream_t st) {
+    using V = Vec<T>;
+    const bool vec_ok = hidden % V::kElems == 0 && aligned16(x) && aligned16(out) && (bias == nullptr || aligned16(bias)) &&
+                        (!kBwd || aligned16(g));
+    if (!vec_ok) {
+        bias_act_generic_kernel<T, kBwd><<<static_cast<int>((hidden + 255) / 256), 256, 0, st>>>(
+            static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(g), static_cast<T*>(out), static_cast<T*>(dbias),
+            rows, hidden, act);
+        return launch_status();
+    }
+    const int nvec = static_cast<int>(hidden / V::kElems);
+    const int col_tiles = (nvec + kBaThreads * kBaVpl - 1) / (kBaThreads * kBaVpl);
+    const int parts = row_parts(rows, col_tiles);
+    const bool need_partial = kBwd && bias != nullptr;
+    if (need_partial && (scratch == nullptr || !aligned16(scratch) || scratch_bytes < static_cast<int64_t>(parts) * hidden * 4))
+        return B200K_ESCRATCH;
+    const dim3 grid(parts, col_tiles);
+    auto go = [&](auto kernel) {
+        kernel<<<grid, kBaThreads, 0, st>>>(static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(g),
+                                           static_cast<T*>(out), static_cast<float*>(scratch), rows, nvec);
+        return launch_status();
+    };
+    int rc;
+    if (bias != nullptr) {
+        rc = act == 0 ? go(bias_act_kernel<T, 0, true, kBwd>) : act == 1 ? go(bias_act_kernel<T, 1, true, kBwd>) : go(bias_act_kernel<T, 2, true, kBwd>);
+    } else {
+        rc = act == 0 ? go(bias_act_kernel<T, 0, false, kBwd>) : act == 1 ? go(bias_act_kernel<T, 1, false, kBwd>) : go(bias_act_kernel<T, 2, false, kBwd>);
+    }
+    if (rc != 0 || !need_partial) return rc;
+    return launch_colsum_finalize<T>(scratch, dbias, parts, hidden, st);
+}
+
+}  // namespace
+}  // namespace b200k
+
+using namespace b200k;
+
+extern "C" int64_t b200k_bias_act_bwd_scratch_bytes(int64_t rows, int64_t hidden) {
+    if (rows <= 0 || hidden <= 0) return 0;
+    int64_t parts = static_cast<int64_t>(sm_count()) * kBaRowParts;
+    if (rows < parts) parts = rows;
+    return parts * hidden * 4;
+}
+
+extern "C" int b200k_bias_act_fwd(const void* x, const void* bias, void* out, int64_t rows, int64_t hidden, int act, int dtype,
+                                  void* stream) {
+    if (rows < 0 || hidden <= 0 || act < 0 || act > 2) return B200K_EINVAL;
+    if (rows == 0) return 0;
+    if (x == nullptr || out == nullptr) return B200K_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (dtype) {
+        case B200K_F32: return run<float, false>(x, bias, nullptr, out, nullptr, nullptr, 0, rows, hidden, act, st);
+        case B200K_BF16: return run<__nv_bfloat16, false>(x, bias, nullptr, out, nullptr, nullptr, 0, rows, hidden, act, st);
+        case B200K_F16: return run<__half, false>(x, bias, nullptr, out, nullptr, nullptr, 0, rows, hidden, act, st);
+        default: return B200K_EDTYPE;
+    }
+}
+
+extern "C" int b200k_bias_act_bwd(const void* x, const void* bias, const void* g, void* dx, void* dbias, void* scratch,
+                                  int64_t scratch_bytes, int64_t rows, int64_t hidden, int act, int dtype, void* stream) {
+    if (rows < 0 || hidden <= 0 || act < 0 || act > 2) return B200K_EINVAL;
+    if (bias != nullptr && dbias == nullptr) return B200K_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (rows == 0) {
+        if (bias != nullptr) {
+            cudaError_t e = cudaMemsetAsync(dbias, 0, static_cast<size_t>(hidden) * (dtype == B200K_F32 ? 4 : 2), st);
+            return e == cudaSuccess ? 0 : static_cast<int>(e);
+        }
+        return 0;
+    }
+    if (x == nullptr || g == nullptr || dx == nullptr) return B200K_EINVAL;
+    switch (dtype) {
+        case B200K_F32: return run<float, true>(x, bias, g, dx, dbias, scratch, scratch_bytes, rows, hidden, act, st);
+        case B200K_BF16: return run<__nv_bfloat16, true>(x, bias, g, dx, dbias, scratch, scratch_bytes, rows, hidden, act, st);
+        case B200K_F16: return run<__half, true>(x, bias, g, dx, dbias, scratch, scratch_bytes, rows, hidden, act, st);
+        default: return B200K_EDTYPE;
+    }
+}
