@@ -173,6 +173,58 @@ B200K_API int64_t b200k_bias_act_bwd_scratch_bytes(int64_t rows, int64_t hidden)
 B200K_API int b200k_bias_act_bwd(const void* x, const void* bias, const void* g, void* dx, void* dbias, void* scratch,
                                  int64_t scratch_bytes, int64_t rows, int64_t hidden, int act, int dtype, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Generic pointwise region — SURVEY §8 rows a3/a4.  Executes a fused region made only of elementwise
+ * prims, convert_element_type and broadcast_in_dim (the claimable vocabulary of
+ * thunder/executors/nvfuserex_impl.py:971-2514 restricted to pointwise work) as ONE pass over memory:
+ * a small register program interpreted per 4-element vector, fp32 arithmetic, explicit rounding
+ * instructions where the trace converts to a 16-bit dtype.  The b200 executor compiles the region's
+ * bound symbols to this program (b200ex/pointwise.py); regions it recognises as a known family go to
+ * the specialised entry points above instead.
+ *
+ * Iteration space: a 3-D box [d0, d1, d2] (the broadcast output shape with adjacent dims merged).
+ * Every operand gives element strides (s0, s1) for the outer dims and `inner`, its element stride along d2
+ * (1 = unit stride, 0 = broadcast; any other value selects the scalar kernel).  Outputs need inner = 1.
+ * Registers 0 .. n_in-1 are preloaded with the inputs converted to fp32; output k stores register
+ * out_reg[k] converted (round-to-nearest-even) to its dtype.  Bool tensors use B200K_BOOL (1 byte, 0/1);
+ * comparison results are 0.0f / 1.0f.
+ *
+ * Instruction word: op | dst << 8 | a << 16 | b << 24.  B200K_PW_CONST and B200K_PW_WHERE take one extra
+ * word (the fp32 bit pattern of the constant / the register index c of `where(a, b, c)`).
+ * --------------------------------------------------------------------------------------------- */
+#define B200K_BOOL 3
+#define B200K_PW_MAX_IN 10
+#define B200K_PW_MAX_OUT 6
+#define B200K_PW_MAX_REG 48
+#define B200K_PW_MAX_CODE 192
+
+enum b200k_pw_op {
+    B200K_PW_CONST = 0, B200K_PW_MOV, B200K_PW_ADD, B200K_PW_SUB, B200K_PW_MUL, B200K_PW_DIV, B200K_PW_NEG, B200K_PW_ABS,
+    B200K_PW_EXP, B200K_PW_LOG, B200K_PW_SQRT, B200K_PW_RSQRT, B200K_PW_RECIP, B200K_PW_ERF, B200K_PW_TANH, B200K_PW_POW,
+    B200K_PW_MAX, B200K_PW_MIN, B200K_PW_GT, B200K_PW_GE, B200K_PW_LT, B200K_PW_LE, B200K_PW_EQ, B200K_PW_NE,
+    B200K_PW_WHERE, B200K_PW_RND_BF16, B200K_PW_RND_F16, B200K_PW_AND, B200K_PW_OR, B200K_PW_NOT, B200K_PW_SIGN,
+    B200K_PW_FLOOR, B200K_PW_CEIL, B200K_PW_EXP2, B200K_PW_LOG2, B200K_PW_LOG1P, B200K_PW_EXPM1, B200K_PW_SIN, B200K_PW_COS,
+    B200K_PW_ERFC, B200K_PW_SIGMOID, B200K_PW_TRUNC, B200K_PW_ROUND, B200K_PW_NOP_COUNT
+};
+
+typedef struct b200k_pw_operand {
+    void* ptr;
+    int64_t s0, s1; /* element strides of the two outer dims */
+    int32_t inner;  /* element stride along d2: 1 unit stride, 0 broadcast, else strided (scalar kernel) */
+    int32_t dtype;  /* B200K_F32 / BF16 / F16 / BOOL */
+} b200k_pw_operand;
+
+typedef struct b200k_pw_program {
+    int64_t d0, d1, d2;
+    int32_t n_in, n_out, n_code, n_reg;
+    b200k_pw_operand in[B200K_PW_MAX_IN];
+    b200k_pw_operand out[B200K_PW_MAX_OUT];
+    int32_t out_reg[B200K_PW_MAX_OUT];
+    uint32_t code[B200K_PW_MAX_CODE];
+} b200k_pw_program;
+
+B200K_API int b200k_pointwise(const b200k_pw_program* program /* host pointer */, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

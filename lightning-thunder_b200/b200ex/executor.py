@@ -1,0 +1,936 @@
+"""The ``b200`` fusion executor: a drop-in for the reference's nvFuser executor behind Thunder's own
+plugin API (``thunder.extend.FusionExecutor``, thunder/extend/__init__.py:206-257).
+
+    import thunder, b200ex.executor as b200
+    jfn = thunder.jit(model, executors=[b200.ex])          # or executors=["b200"] after this import
+
+What it does, mirroring thunder/executors/nvfuserex_impl.py:
+
+* **claim** — ``register_supported`` for the pointwise prim vocabulary (elementwise unary/binary/
+  ternary prims, ``convert_element_type``, ``broadcast_in_dim``, ``shallow_copy``) and op-level rules with
+  their own grad transforms for ``ltorch.rms_norm`` and ``ltorch.cross_entropy`` (the pattern of
+  nvfuserex_impl.py:3122-3159), plus the ``qkv_split_rope`` operator (lookaside, extend:146-198).
+* **fusion_pass** — partitions the joint forward+backward trace with the reference's own partitioner
+  (``fuse_bound_symbols``), skips shape-only groups, honours optimization fuel, calls :meth:`fuse`, then
+  runs ``rematerialize`` / ``dce`` / ``update_fusion_call_ctx`` exactly like nvfuserex_impl.py:836-939.
+* **fuse** — flattens a region to claimed symbols and returns a ``b200FusionN`` bound symbol whose
+  callable (:class:`B200Region`) lowers the region to C-ABI launches on first call per
+  (shape, stride, dtype) key: family kernels for the macro ops (fused with an adjacent residual add when
+  the region has one), the native SwiGLU kernels for regions whose canonical program matches, and the
+  generic pointwise interpreter otherwise.  A region it cannot lower is left un-fused for the torch
+  executor; nothing inside a claimed region ever falls back to another backend.
+"""
+
+from __future__ import annotations
+
+import os
+import threading
+import time
+from numbers import Number
+from typing import Any, Callable
+
+import torch
+
+import thunder
+import thunder.torch as ltorch
+from thunder.core import dtypes, prims, utils
+from thunder.core.compile_data import get_compile_option
+from thunder.core.prims import PrimIDs
+from thunder.core.proxies import Proxy, TensorProxy, Variable, unvariableify, variableify
+from thunder.core.rematerialization import rematerialize
+from thunder.core.symbol import BoundSymbol, has_tags
+from thunder.core.trace import TraceCtx, TraceProvenance, from_trace
+from thunder.core.transform_common import dce
+from thunder.core.transforms import get_grad, put_grads
+from thunder.executors.passes import update_fusion_call_ctx
+from thunder.executors.utils import Region
+from thunder.extend import FUEL_LEVEL, FusionExecutor, register_executor
+
+from . import ops
+from .pointwise import PwLaunch, PwNode, PwUnsupported, compile_region
+
+__all__ = ["ex", "B200Executor", "qkv_split_rope", "swiglu"]
+
+_TORCH_DTYPE = {dtypes.float32: torch.float32, dtypes.bfloat16: torch.bfloat16, dtypes.float16: torch.float16, dtypes.bool8: torch.bool}
+
+
+def _tdtype(d) -> torch.dtype | None:
+    try:
+        return _TORCH_DTYPE.get(dtypes.to_strong_dtype(d)) if d is not None else None
+    except Exception:
+        return None
+
+
+# Tests that inspect trace structure on a machine without a GPU flip this so that the checkers accept CPU
+# proxies.  It only affects claiming: executing a claimed region on CPU tensors still raises (no CPU path).
+_CLAIM_CPU_FOR_TESTS = False
+
+
+def _testing_claim_cpu(flag: bool) -> None:
+    global _CLAIM_CPU_FOR_TESTS
+    _CLAIM_CPU_FOR_TESTS = bool(flag)
+
+
+def _is_cuda_float(p, allow_bool=False) -> bool:
+    if not isinstance(p, TensorProxy):
+        return False
+    if p.device.devicetype is not thunder.core.devices.DeviceType.CUDA and not _CLAIM_CPU_FOR_TESTS:
+        return False
+    dt = _tdtype(p.dtype)
+    return dt is not None and (allow_bool or dt is not torch.bool)
+
+
+# --------------------------------------------------------------------------------------------------
+# The executor
+# --------------------------------------------------------------------------------------------------
+class B200Executor(FusionExecutor):
+    _optimization_fuel: int | FUEL_LEVEL
+
+    def __init__(self):
+        from . import __version__
+
+        super().__init__("b200", version=__version__)
+        fuel = os.getenv("B200EX_OPTIMIZATION_FUEL")
+        self.set_fuel(int(fuel) if fuel else FUEL_LEVEL.UNLIMITED)
+        self._use_rematerialization = True
+
+    # -- optimization fuel (extend/__init__.py:201-226; nvfuserex_impl.py:658-675) ----------------
+    def get_fuel(self, amount: int = 1, /) -> bool:
+        if self._optimization_fuel is FUEL_LEVEL.UNLIMITED:
+            return True
+        if self._optimization_fuel < amount:
+            return False
+        self._optimization_fuel -= amount
+        return True
+
+    def set_fuel(self, value: int | FUEL_LEVEL):
+        if isinstance(value, FUEL_LEVEL):
+            self._optimization_fuel = value
+            return
+        if not isinstance(value, int) or value < 0:
+            raise ValueError(f"optimization fuel must be a non-negative int, got {value!r}")
+        self._optimization_fuel = value
+
+    # -- region construction ------------------------------------------------------------------------
+    def flatten(self, bsym: BoundSymbol) -> list[BoundSymbol]:
+        """Descend into subsymbols until every bound symbol is one this executor claims directly."""
+        if self.can_execute(bsym):
+            return [bsym]
+        utils.check(
+            len(bsym.subsymbols) > 0,
+            lambda: f"b200 cannot flatten {bsym.sym.name}: not supported and it has no subsymbols",
+            exception_type=AssertionError,
+        )
+        out: list[BoundSymbol] = []
+        for s in bsym.subsymbols:
+            out.extend(self.flatten(s))
+        return out
+
+    @staticmethod
+    def _has_cuda_tensor(bsym: BoundSymbol) -> bool:
+        for p in list(bsym.flat_proxy_args) + list(bsym.flat_proxy_outs):
+            if isinstance(p, TensorProxy) and (p.device.devicetype is thunder.core.devices.DeviceType.CUDA or _CLAIM_CPU_FOR_TESTS):
+                return True
+        return False
+
+    def _dce_bsyms(self, inputs: list, outputs: list, bsyms: list[BoundSymbol]) -> list[BoundSymbol]:
+        trace = TraceCtx(None)
+        trace.bound_symbols = list(bsyms) + [prims.python_return.bind(outputs, output=None)]
+        needed: set[Variable] = set()
+        trace = dce(trace, needed)
+        inputs[:] = [x for x in inputs if variableify(x) in needed]
+        return [b for b in trace.bound_symbols if b.sym != prims.python_return]
+
+    def fuse(self, region: Region, fusion_counter: int) -> BoundSymbol:
+        inputs: list[Proxy] = [unvariableify(x) for x in region.inputs]
+        outputs: list[Proxy] = [unvariableify(x) for x in region.outputs]
+        flat: list[BoundSymbol] = []
+        for b in region.bound_symbols:
+            flat.extend(self.flatten(b))
+        flat = self._dce_bsyms(inputs, outputs, flat)
+        name = f"b200Fusion{fusion_counter}"
+        fn = B200Region(name, flat, inputs, outputs)
+        return self.register_temporary_operation(name, fn, inputs=inputs, outputs=outputs, bsyms=flat)
+
+    def can_lower(self, bsyms: list[BoundSymbol]) -> bool:
+        """Cheap structural check used by the fusion pass: would :class:`B200Region` accept this group?"""
+        try:
+            flat: list[BoundSymbol] = []
+            for b in bsyms:
+                flat.extend(self.flatten(b))
+            return all(b.sym.id in _MACRO_IMPL or b.sym.id in _PW_OPNAME for b in flat)
+        except AssertionError:
+            return False
+
+    # -- the pass (nvfuserex_impl.py:836-939) ---------------------------------------------------------
+    def fusion_pass(self, trace: TraceCtx) -> TraceCtx:
+        start = time.perf_counter_ns()
+        from thunder.executors.data_dependent_partition import Node, fuse_bound_symbols
+
+        fusedtrace: TraceCtx = from_trace(trace)
+        producers, consumers = utils.producers_and_consumers(trace)
+
+        def _can_fuse_node(n: Node) -> bool:
+            if len(n.group_bsyms) > 1:
+                return True
+            b = n.group_bsyms[0]
+            return self.can_fuse(b) and self._has_cuda_tensor(b)
+
+        groups = fuse_bound_symbols(trace, lambda a, b: _can_fuse_node(a) and _can_fuse_node(b))
+        enable_shape_only = get_compile_option("b200_enable_shape_only_fusion", "Let b200 fuse regions made only of shape operations. Defaults to False.")
+        min_region = get_compile_option("b200_min_region_size", "Smallest number of bound symbols b200 turns into a fusion. Defaults to 1.") or 1
+
+        fused: list[BoundSymbol] = []
+        counter = 0
+        for bsyms in groups:
+            if not enable_shape_only and all(_all_tagged(b, prims.OpTags.SHAPE_OP) for b in bsyms):
+                fused.extend(bsyms)
+                continue
+            if len(bsyms) == 1:
+                b = bsyms[0]
+                if not (self.can_fuse(b) and self._has_cuda_tensor(b)):
+                    fused.append(b)
+                    continue
+            if len(bsyms) < min_region or not self.can_lower(bsyms):
+                fused.extend(bsyms)
+                continue
+            if self.get_fuel():
+                region = Region(producers, consumers, bsyms)
+                try:
+                    fused.append(self.fuse(region, counter))
+                    counter += 1
+                except PwUnsupported:
+                    fused.extend(bsyms)  # decline: the torch executor runs these
+            else:
+                fused.extend(bsyms)
+        fusedtrace.bound_symbols = fused
+
+        if self._use_rematerialization:
+            fusedtrace = rematerialize(fusedtrace)
+        fusedtrace = dce(fusedtrace)
+        fusedtrace = update_fusion_call_ctx(fusedtrace)
+        ms = (time.perf_counter_ns() - start) // 1000000
+        fusedtrace.set_provenance(TraceProvenance(f"b200 fusion (took {ms} milliseconds)"))
+        return fusedtrace
+
+
+def _all_tagged(bsym: BoundSymbol, tag) -> bool:
+    if not has_tags(bsym, {tag}):
+        return False
+    return all(has_tags(s, {tag}) for s in bsym.subsymbols)
+
+
+ex = B200Executor()
+register_executor(ex)
+
+
+# --------------------------------------------------------------------------------------------------
+# Pointwise vocabulary (restricted to what b200k_pointwise executes)
+# --------------------------------------------------------------------------------------------------
+_PW_OPNAME: dict[Any, str] = {
+    PrimIDs.ADD: "add", PrimIDs.SUB: "sub", PrimIDs.MUL: "mul", PrimIDs.DIV: "div", PrimIDs.POW: "pow",
+    PrimIDs.MAXIMUM: "maximum", PrimIDs.MINIMUM: "minimum",
+    PrimIDs.GT: "gt", PrimIDs.GE: "ge", PrimIDs.LT: "lt", PrimIDs.LE: "le", PrimIDs.EQ: "eq", PrimIDs.NE: "ne",
+    PrimIDs.NEG: "neg", PrimIDs.ABS: "abs", PrimIDs.EXP: "exp", PrimIDs.LOG: "log", PrimIDs.SQRT: "sqrt", PrimIDs.RSQRT: "rsqrt",
+    PrimIDs.RECIPROCAL: "reciprocal", PrimIDs.ERF: "erf", PrimIDs.TANH: "tanh", PrimIDs.SIGN: "sign", PrimIDs.FLOOR: "floor",
+    PrimIDs.CEIL: "ceil", PrimIDs.EXP2: "exp2", PrimIDs.LOG2: "log2", PrimIDs.LOG1P: "log1p", PrimIDs.EXPM1: "expm1",
+    PrimIDs.SIN: "sin", PrimIDs.COS: "cos", PrimIDs.ERFC: "erfc", PrimIDs.TRUNC: "trunc", PrimIDs.ROUND: "round",
+    PrimIDs.WHERE: "where", PrimIDs.CONVERT_ELEMENT_TYPE: "convert", PrimIDs.BROADCAST_IN_DIM: "broadcast_in_dim",
+    PrimIDs.SHALLOW_COPY: "mov", PrimIDs.CLONE: "mov",
+}
+
+
+def _pw_scalar_ok(x) -> bool:
+    return isinstance(x, (bool, int, float)) and not isinstance(x, Proxy)
+
+
+def _pw_check(*args, **kwargs) -> bool:
+    """Elementwise prim: every tensor operand is a CUDA fp32/bf16/fp16/bool tensor and every other operand
+    a plain Python number (a NumberProxy would need a host sync or a recompile per value)."""
+    saw_tensor = False
+    for a in args:
+        if isinstance(a, TensorProxy):
+            if not _is_cuda_float(a, allow_bool=True):
+                return False
+            saw_tensor = True
+        elif not _pw_scalar_ok(a):
+            return False
+    return saw_tensor and not kwargs
+
+
+def _convert_check(a, dtype) -> bool:
+    return isinstance(a, TensorProxy) and _is_cuda_float(a, allow_bool=True) and _tdtype(dtype) is not None
+
+
+def _broadcast_check(a, shape, broadcast_dimensions) -> bool:
+    return (
+        isinstance(a, TensorProxy) and _is_cuda_float(a, allow_bool=True) and all(isinstance(s, int) for s in shape)
+        and list(broadcast_dimensions) == sorted(broadcast_dimensions)
+    )
+
+
+for _pid in _PW_OPNAME:
+    if _pid is PrimIDs.CONVERT_ELEMENT_TYPE:
+        ex.register_supported(_pid, _convert_check)
+    elif _pid is PrimIDs.BROADCAST_IN_DIM:
+        ex.register_supported(_pid, _broadcast_check)
+    else:
+        ex.register_supported(_pid, _pw_check)
+
+
+# --------------------------------------------------------------------------------------------------
+# Macro ops: RMSNorm, cross-entropy, QKV-split RoPE, SwiGLU.  Each is an executor operator with a Python
+# implementation (a C-ABI launcher), so it runs on its own when it ends up outside a fusion, and is also
+# claimed by the fusion pass so that neighbouring pointwise work can be folded into the same launch.
+# --------------------------------------------------------------------------------------------------
+def _rms_norm_fwd_meta(a, weight, eps):
+    y = TensorProxy(like=a)
+    rstd = TensorProxy(like=a, shape=tuple(a.shape[:-1]) + (1,), dtype=dtypes.float32)
+    return y, rstd
+
+
+def _rms_norm_fwd_impl(a, weight, eps):
+    _, y, rstd = ops.rmsnorm_fwd(a, None, weight, eps)
+    return y, rstd
+
+
+def _rms_norm_bwd_meta(dy, a, weight, rstd):
+    da = TensorProxy(like=a)
+    dw = TensorProxy(like=weight) if weight is not None else None
+    return da, dw
+
+
+def _rms_norm_bwd_impl(dy, a, weight, rstd):
+    return ops.rmsnorm_bwd(dy, a, weight, rstd, None)
+
+
+b200_rms_norm_fwd = ex.register_operator("b200_rms_norm_fwd", meta=_rms_norm_fwd_meta, fn=_rms_norm_fwd_impl, tags=[prims.OpTags.REDUCTION_OP])
+b200_rms_norm_bwd = ex.register_operator("b200_rms_norm_bwd", meta=_rms_norm_bwd_meta, fn=_rms_norm_bwd_impl, tags=[prims.OpTags.REDUCTION_OP])
+
+
+def _rms_norm_check(a, /, normalized_shape, weight=None, eps=None) -> bool:
+    if not _is_cuda_float(a) or a.ndim < 1:
+        return False
+    if len(normalized_shape) != 1 or normalized_shape[0] != a.shape[-1]:
+        return False
+    if weight is not None and (not _is_cuda_float(weight) or weight.dtype != a.dtype or tuple(weight.shape) != (a.shape[-1],)):
+        return False
+    return eps is None or isinstance(eps, float)
+
+
+def _rms_eps(a, eps):
+    return float(torch.finfo(torch.float32).eps) if eps is None else float(eps)  # ltorch upcasts 16-bit inputs first
+
+
+def _rms_norm_transform(a, /, normalized_shape, weight=None, eps=None):
+    y, _ = b200_rms_norm_fwd(a, weight, _rms_eps(a, eps))
+    return y
+
+
+def _rms_norm_grad(a, /, normalized_shape, weight=None, eps=None):
+    y, rstd = b200_rms_norm_fwd(a, weight, _rms_eps(a, eps))
+    g = get_grad(y)
+    da, dw = b200_rms_norm_bwd(g, a, weight, rstd)
+    put_grads((a,), (da,))
+    if weight is not None:
+        put_grads((weight,), (dw,))
+    return y
+
+
+ex.register_supported(b200_rms_norm_fwd.id)
+ex.register_supported(b200_rms_norm_bwd.id)
+ex.register_supported(ltorch.rms_norm, _rms_norm_check, execution_transform=_rms_norm_transform, grad_transform=_rms_norm_grad)
+
+
+# ---- cross-entropy ---------------------------------------------------------------------------------
+def _ce_fwd_meta(a, target, ignore_index, reduction):
+    loss = TensorProxy(like=a, shape=())
+    row_max = TensorProxy(like=a, shape=(a.shape[0],), dtype=dtypes.float32)
+    row_logsum = TensorProxy(like=a, shape=(a.shape[0],), dtype=dtypes.float32)
+    n_valid = TensorProxy(like=target, shape=(), dtype=dtypes.int64)
+    return loss, row_max, row_logsum, n_valid
+
+
+def _ce_fwd_impl(a, target, ignore_index, reduction):
+    return ops.cross_entropy_fwd(a, target, ignore_index, reduction)
+
+
+def _ce_bwd_meta(g, a, target, row_max, row_logsum, n_valid, ignore_index, reduction):
+    return TensorProxy(like=a)
+
+
+def _ce_bwd_impl(g, a, target, row_max, row_logsum, n_valid, ignore_index, reduction):
+    return ops.cross_entropy_bwd(g, a, target, row_max, row_logsum, n_valid, ignore_index, reduction)
+
+
+b200_cross_entropy_fwd = ex.register_operator("b200_cross_entropy_fwd", meta=_ce_fwd_meta, fn=_ce_fwd_impl, tags=[prims.OpTags.REDUCTION_OP])
+b200_cross_entropy_bwd = ex.register_operator("b200_cross_entropy_bwd", meta=_ce_bwd_meta, fn=_ce_bwd_impl)
+
+
+def _ce_check(a, /, target, weight=None, size_average=None, ignore_index=-100, reduce=None, reduction="mean", label_smoothing=0.0) -> bool:
+    # Same restrictions as the reference's fused rule (nvfuserex_impl.py:2900-2940) except that 16-bit logits
+    # and non-negative ignore_index are fine here.
+    if not _is_cuda_float(a) or a.ndim != 2:
+        return False
+    if not isinstance(target, TensorProxy) or target.ndim != 1 or target.shape[0] != a.shape[0]:
+        return False
+    if dtypes.to_strong_dtype(target.dtype) != dtypes.int64:
+        return False
+    if reduction not in ("mean", "sum") or not isinstance(ignore_index, int):
+        return False
+    if any(x is not None for x in (weight, size_average, reduce)) or label_smoothing != 0.0:
+        return False
+    return True
+
+
+def _ce_transform(a, /, target, weight=None, size_average=None, ignore_index=-100, reduce=None, reduction="mean", label_smoothing=0.0):
+    loss, _, _, _ = b200_cross_entropy_fwd(a, target, ignore_index, reduction)
+    return loss
+
+
+def _ce_grad(a, /, target, weight=None, size_average=None, ignore_index=-100, reduce=None, reduction="mean", label_smoothing=0.0):
+    loss, row_max, row_logsum, n_valid = b200_cross_entropy_fwd(a, target, ignore_index, reduction)
+    g = get_grad(loss)
+    da = b200_cross_entropy_bwd(g, a, target, row_max, row_logsum, n_valid, ignore_index, reduction)
+    put_grads((a,), (da,))
+    return loss
+
+
+ex.register_supported(b200_cross_entropy_fwd.id)
+ex.register_supported(b200_cross_entropy_bwd.id)
+ex.register_supported(ltorch.cross_entropy, _ce_check, execution_transform=_ce_transform, grad_transform=_ce_grad)
+
+
+# ---- QKV split + RoPE (lookaside on a plain PyTorch function; extend/__init__.py `replaces=`) ----------
+def _qkv_split_rope_body(cat, qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem):
+    B, T, _ = qkv.shape
+    q_per_kv = n_head // n_query_groups
+    t = qkv.view(B, T, n_query_groups, q_per_kv + 2, head_size).permute(0, 2, 3, 1, 4)
+    q, k, v = t.split((q_per_kv, 1, 1), dim=2)
+    if n_query_groups != n_head and n_query_groups != 1:
+        k = k.expand(B, n_query_groups, q_per_kv, T, head_size)
+        v = v.expand(B, n_query_groups, q_per_kv, T, head_size)
+    q = q.reshape(B, -1, T, head_size)
+    k = k.reshape(B, -1, T, head_size)
+    v = v.reshape(B, -1, T, head_size)
+
+    def rope(x):
+        half = x.shape[-1] // 2
+        rotated = cat((-x[..., half:], x[..., :half]), dim=-1)
+        return ((x * cos) + (rotated * sin)).to(dtype=x.dtype)
+
+    q_roped = rope(q[..., :rope_n_elem])
+    k_roped = rope(k[..., :rope_n_elem])
+    q = cat((q_roped, q[..., rope_n_elem:]), dim=-1)
+    k = cat((k_roped, k[..., rope_n_elem:]), dim=-1)
+    return q, k, v
+
+
+def qkv_split_rope(qkv: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, n_head: int, n_query_groups: int, head_size: int, rope_n_elem: int):
+    """The LitGPT attention slice the reference vendors at thunder/benchmarks/__init__.py:2282-2328, as plain
+    PyTorch.  Models call this function; with ``b200`` in the executor list Thunder swaps in the fused
+    operator (whose decomposition is the same code over thunder.torch), without it the function traces or
+    runs eagerly as ordinary torch ops."""
+    return _qkv_split_rope_body(torch.cat, qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
+
+
+def _qkv_split_rope_like(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem):
+    return _qkv_split_rope_body(ltorch.cat, qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
+
+
+def _kv_heads(n_head, groups):
+    return n_head if (groups != n_head and groups != 1) else groups
+
+
+def _rope_bwd_meta(dq, dk, dv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem):
+    B, T = dq.shape[0], dq.shape[2]
+    return TensorProxy(like=dq, shape=(B, T, (n_head + 2 * n_query_groups) * head_size))
+
+
+def _rope_runtime_ok(qkv, cos, sin) -> bool:
+    return all(isinstance(t, torch.Tensor) and t.is_cuda and t.dtype in ops.DTYPE_CODE for t in (qkv, cos, sin)) and qkv.dtype == cos.dtype == sin.dtype
+
+
+def _rope_fwd_impl(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem):
+    # Thunder keeps an executor-owned symbol even when its checker declined it (passes.py:78-81), so the
+    # callable has to cope with inputs outside the kernel's domain: those run the plain PyTorch definition.
+    if _rope_runtime_ok(qkv, cos, sin):
+        return ops.qkv_rope_fwd(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
+    return qkv_split_rope(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
+
+
+b200_qkv_split_rope = ex.register_operator("b200_qkv_split_rope", like=_qkv_split_rope_like, fn=_rope_fwd_impl, replaces=qkv_split_rope)
+b200_qkv_rope_bwd = ex.register_operator("b200_qkv_rope_bwd", meta=_rope_bwd_meta, fn=ops.qkv_rope_bwd)
+
+
+def _rope_check(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem) -> bool:
+    if not (_is_cuda_float(qkv) and _is_cuda_float(cos) and _is_cuda_float(sin)) or qkv.ndim != 3:
+        return False
+    if cos.dtype != qkv.dtype or sin.dtype != qkv.dtype or cos.ndim != 2 or tuple(cos.shape) != tuple(sin.shape):
+        return False
+    if not all(isinstance(v, int) for v in (n_head, n_query_groups, head_size, rope_n_elem)):
+        return False
+    return (
+        n_head % n_query_groups == 0 and qkv.shape[2] == (n_head + 2 * n_query_groups) * head_size
+        and rope_n_elem % 2 == 0 and 0 <= rope_n_elem <= head_size and tuple(cos.shape) == (qkv.shape[1], rope_n_elem)
+    )
+
+
+def _rope_grad(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem):
+    q, k, v = b200_qkv_split_rope(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
+    dq, dk, dv = get_grad(q), get_grad(k), get_grad(v)
+    dqkv = b200_qkv_rope_bwd(dq, dk, dv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
+    put_grads((qkv,), (dqkv,))
+    return q, k, v
+
+
+ex.register_supported(b200_qkv_split_rope.id, _rope_check, grad_transform=_rope_grad)
+ex.register_supported(b200_qkv_rope_bwd.id)
+
+
+# ---- SwiGLU: op-level for models that call b200ex.swiglu; `F.silu(a) * b` written inline is recognised
+#      inside pointwise regions instead (see _native_for) ---------------------------------------------------
+def swiglu(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """``silu(a) * b`` as plain PyTorch (LLaMAMLP's activation)."""
+    return torch.nn.functional.silu(a) * b
+
+
+def _swiglu_runtime_ok(*ts) -> bool:
+    return all(isinstance(t, torch.Tensor) and t.is_cuda and t.dtype in ops.DTYPE_CODE and t.shape == ts[0].shape and t.dtype == ts[0].dtype for t in ts)
+
+
+def _swiglu_fwd_impl(a, b):
+    return ops.swiglu_fwd(a, b) if _swiglu_runtime_ok(a, b) else swiglu(a, b)
+
+
+def _swiglu_bwd_meta(a, b, g):
+    return TensorProxy(like=a), TensorProxy(like=b)
+
+
+def _swiglu_like(a, b):
+    return ltorch.silu(a) * b
+
+
+b200_swiglu = ex.register_operator("b200_swiglu", like=_swiglu_like, fn=_swiglu_fwd_impl, replaces=swiglu)
+b200_swiglu_bwd = ex.register_operator("b200_swiglu_bwd", meta=_swiglu_bwd_meta, fn=ops.swiglu_bwd)
+
+
+def _swiglu_check(a, b) -> bool:
+    return _is_cuda_float(a) and _is_cuda_float(b) and a.dtype == b.dtype and tuple(a.shape) == tuple(b.shape)
+
+
+def _swiglu_grad(a, b):
+    out = b200_swiglu(a, b)
+    g = get_grad(out)
+    da, db = b200_swiglu_bwd(a, b, g)
+    put_grads((a, b), (da, db))
+    return out
+
+
+ex.register_supported(b200_swiglu.id, _swiglu_check, grad_transform=_swiglu_grad)
+ex.register_supported(b200_swiglu_bwd.id)
+
+
+_MACRO_IMPL: dict[Any, Callable] = {
+    b200_rms_norm_fwd.id: _rms_norm_fwd_impl,
+    b200_rms_norm_bwd.id: _rms_norm_bwd_impl,
+    b200_cross_entropy_fwd.id: _ce_fwd_impl,
+    b200_cross_entropy_bwd.id: _ce_bwd_impl,
+    b200_qkv_split_rope.id: _rope_fwd_impl,
+    b200_qkv_rope_bwd.id: ops.qkv_rope_bwd,
+    b200_swiglu.id: _swiglu_fwd_impl,
+    b200_swiglu_bwd.id: ops.swiglu_bwd,
+}
+
+
+# --------------------------------------------------------------------------------------------------
+# Region lowering and launch (the role of FusionDefinitionWrapper, nvfuserex_impl.py:526-576)
+# --------------------------------------------------------------------------------------------------
+def _descriptor(args) -> tuple:
+    """Cache key of a call: (shape, stride, dtype) per tensor, the value per number — the analogue of
+    to_runtime_descriptors (nvfuserex_impl.py:505-521), needed because proxies carry no strides."""
+    key = []
+    for a in args:
+        if isinstance(a, torch.Tensor):
+            key.append((tuple(a.shape), a.stride(), a.dtype, a.device.index))
+        else:
+            key.append((type(a), a))
+    return tuple(key)
+
+
+class _Step:
+    """One launch (or one zero-copy alias) of a lowered region."""
+
+    __slots__ = ("run", "kind")
+
+    def __init__(self, kind: str, run: Callable[[dict], None]):
+        self.kind, self.run = kind, run
+
+
+def _outs_of(b: BoundSymbol) -> list[Proxy]:
+    return [o for o in b.flat_proxy_outs]
+
+
+class B200Region:
+    """Callable installed in the trace for one fusion.
+
+    Lowering is dataflow driven, not positional (after rematerialisation the bound symbols of unrelated
+    chains interleave):
+
+    1. redundant casts (``bf16 -> f32 -> bf16``, same-dtype converts, shallow copies) become aliases — the
+       job of ``remove_redundant_casts`` in the reference (nvfuserex_impl.py:2281-2434);
+    2. a residual add feeding ``b200_rms_norm_fwd`` / fed by ``b200_rms_norm_bwd`` is folded into the norm
+       kernel (the fused RMSNorm+residual region of SURVEY §8 a5/a6);
+    3. everything else is scheduled greedily: all pointwise work whose inputs are available forms one wave,
+       split into connected components, each compiled to one program per output shape (a component whose
+       canonical program is a known family runs that family's kernel); then the ready macro ops run.
+    """
+
+    def __init__(self, name: str, bsyms: list[BoundSymbol], inputs: list[Proxy], outputs: list[Proxy]):
+        self.name = name
+        self.bsyms = bsyms
+        self.input_names = [p.name for p in inputs]
+        self.output_names = [p.name for p in outputs]
+        self.alias: dict[str, str] = {}
+        self.steps = self._lower()
+        self.launch_kinds = [s.kind for s in self.steps]
+
+    def __repr__(self):
+        return f"B200Region({self.name}: {', '.join(self.launch_kinds)})"
+
+    # ---- helpers ------------------------------------------------------------------------------------------
+    def _resolve(self, name: str) -> str:
+        while name in self.alias:
+            name = self.alias[name]
+        return name
+
+    def _find_aliases(self, prod: dict[str, BoundSymbol]) -> set[int]:
+        """Marks bound symbols that only rename a value.  Returns their ids."""
+        dead: set[int] = set()
+        for b in self.bsyms:
+            sid = b.sym.id
+            if sid == PrimIDs.SHALLOW_COPY and isinstance(b.args[0], TensorProxy):
+                self.alias[b.output.name] = b.args[0].name
+                dead.add(id(b))
+            elif sid == PrimIDs.CONVERT_ELEMENT_TYPE and isinstance(b.args[0], TensorProxy):
+                src, out = b.args[0], b.output
+                if _tdtype(src.dtype) is _tdtype(out.dtype):
+                    self.alias[out.name] = src.name
+                    dead.add(id(b))
+                    continue
+                # narrow -> f32 -> same narrow dtype is the identity
+                inner = prod.get(src.name)
+                if (
+                    inner is not None and inner.sym.id == PrimIDs.CONVERT_ELEMENT_TYPE and isinstance(inner.args[0], TensorProxy)
+                    and _tdtype(src.dtype) is torch.float32 and _tdtype(inner.args[0].dtype) is _tdtype(out.dtype)
+                    and _tdtype(out.dtype) in (torch.bfloat16, torch.float16)
+                ):
+                    self.alias[out.name] = inner.args[0].name
+                    dead.add(id(b))
+        return dead
+
+    def _arg_names(self, b: BoundSymbol) -> list[str]:
+        return [self._resolve(p.name) for p in b.flat_proxy_args]
+
+    # ---- lowering -----------------------------------------------------------------------------------------
+    def _lower(self) -> list[_Step]:
+        prod: dict[str, BoundSymbol] = {o.name: b for b in self.bsyms for o in _outs_of(b)}
+        dead = self._find_aliases(prod)
+        live = [b for b in self.bsyms if id(b) not in dead]
+        consumers: dict[str, list[BoundSymbol]] = {}
+        for b in live:
+            for n in self._arg_names(b):
+                consumers.setdefault(n, []).append(b)
+        region_outs = {self._resolve(n) for n in self.output_names}
+
+        absorbed: set[int] = set()
+        macro_steps: dict[int, tuple] = {}  # id(bsym) -> (step, input names, output names)
+        for b in live:
+            if b.sym.id not in _MACRO_IMPL:
+                continue
+            fused = self._try_residual_fusion(b, prod, consumers, region_outs, absorbed)
+            macro_steps[id(b)] = fused if fused is not None else self._macro_step(b)
+
+        steps: list[_Step] = []
+        available = set(self.input_names)
+        remaining = [b for b in live if id(b) not in absorbed]
+        while remaining:
+            progressed = False
+            # wave of pointwise work: every node whose inputs are available or produced inside the wave
+            wave, wave_out = [], set()
+            for b in remaining:
+                if b.sym.id in _MACRO_IMPL:
+                    continue
+                if all(n in available or n in wave_out for n in self._arg_names(b)):
+                    wave.append(b)
+                    wave_out.update(o.name for o in _outs_of(b))
+            if wave:
+                wave_ids = {id(b) for b in wave}
+                later = [b for b in remaining if id(b) not in wave_ids]
+                needed = set(region_outs)
+                for b in later:
+                    if b.sym.id not in _MACRO_IMPL:
+                        needed.update(self._arg_names(b))
+                for _, ins, _ in macro_steps.values():
+                    needed.update(ins)
+                steps.extend(self._lower_wave(wave, needed))
+                available |= wave_out
+                remaining = later
+                progressed = True
+            for b in list(remaining):
+                if b.sym.id in _MACRO_IMPL:
+                    step, ins, outs = macro_steps[id(b)]
+                    if all(n in available for n in ins):
+                        steps.append(step)
+                        available.update(outs)
+                        remaining.remove(b)
+                        progressed = True
+            if not progressed:
+                raise PwUnsupported(f"{self.name}: cannot schedule region (cyclic or unknown dependency)")
+        return steps
+
+    def _macro_step(self, b: BoundSymbol):
+        impl = _MACRO_IMPL[b.sym.id]
+        arg_spec = [(self._resolve(a.name) if isinstance(a, Proxy) else None, a) for a in b.args]
+        kw_spec = {k: ((self._resolve(v.name) if isinstance(v, Proxy) else None), v) for k, v in b.kwargs.items()}
+        outs = b.output if isinstance(b.output, (tuple, list)) else (b.output,)
+        out_names = [o.name if isinstance(o, Proxy) else None for o in outs]
+
+        def run(env):
+            args = [env[n] if n is not None else v for n, v in arg_spec]
+            kwargs = {k: (env[n] if n is not None else v) for k, (n, v) in kw_spec.items()}
+            res = impl(*args, **kwargs)
+            res = res if isinstance(res, (tuple, list)) else (res,)
+            for n, r in zip(out_names, res):
+                if n is not None:
+                    env[n] = r
+
+        ins = [n for n, _ in arg_spec if n is not None] + [n for n, _ in kw_spec.values() if n is not None]
+        return _Step(b.sym.name, run), ins, [n for n in out_names if n is not None]
+
+    # ---- residual-add peepholes around RMSNorm (dataflow matches) ----------------------------------------
+    @staticmethod
+    def _single_consumer(name: str, consumers, region_outs):
+        cs = consumers.get(name, [])
+        if len(cs) != 1 or name in region_outs:
+            return None
+        return cs[0]
+
+    def _try_residual_fusion(self, b: BoundSymbol, prod, consumers, region_outs, absorbed: set):
+        lowp = lambda p: _tdtype(p.dtype) in (torch.bfloat16, torch.float16)
+        if b.sym.id == b200_rms_norm_fwd.id:
+            a, weight, eps = b.args
+            hname = self._resolve(a.name)
+            chain: list[BoundSymbol] = []
+            top = prod.get(hname)
+            if top is None:
+                return None
+            if lowp(a):
+                # h = cast(add(cast32(x), cast32(r)))
+                if top.sym.id != PrimIDs.CONVERT_ELEMENT_TYPE or not isinstance(top.args[0], TensorProxy):
+                    return None
+                add = prod.get(self._resolve(top.args[0].name))
+                if add is None or add.sym.id != PrimIDs.ADD or self._single_consumer(add.output.name, consumers, region_outs) is not top:
+                    return None
+                chain += [top, add]
+                srcs = []
+                for t in add.args:
+                    if not isinstance(t, TensorProxy):
+                        return None
+                    c = prod.get(self._resolve(t.name))
+                    if c is None or c.sym.id != PrimIDs.CONVERT_ELEMENT_TYPE or not isinstance(c.args[0], TensorProxy):
+                        return None
+                    if self._single_consumer(c.output.name, consumers, region_outs) is not add:
+                        return None
+                    chain.append(c)
+                    srcs.append(c.args[0])
+            else:
+                if top.sym.id != PrimIDs.ADD:
+                    return None
+                chain.append(top)
+                srcs = list(top.args)
+            if len(srcs) != 2 or not all(isinstance(t, TensorProxy) and tuple(t.shape) == tuple(a.shape) and t.dtype == a.dtype for t in srcs):
+                return None
+            xn, rn = (self._resolve(t.name) for t in srcs)
+            y, rstd = b.output
+            wn = self._resolve(weight.name) if weight is not None else None
+            yn, rsn = y.name, rstd.name
+
+            def run(env):
+                h, yv, rs = ops.rmsnorm_fwd(env[xn], env[rn], env[wn] if wn else None, eps)
+                env[hname], env[yn], env[rsn] = h, yv, rs
+
+            absorbed.update(id(c) for c in chain)
+            return _Step("b200_rms_norm_fwd+residual", run), [n for n in (xn, rn, wn) if n], [hname, yn, rsn]
+        if b.sym.id == b200_rms_norm_bwd.id:
+            dy, a, weight, rstd = b.args
+            da, dw = b.output
+            if lowp(da):
+                # dx = cast(add(cast32(dh_in), cast32(da)))
+                c_da = self._single_consumer(da.name, consumers, region_outs)
+                if c_da is None or c_da.sym.id != PrimIDs.CONVERT_ELEMENT_TYPE:
+                    return None
+                add = self._single_consumer(c_da.output.name, consumers, region_outs)
+                if add is None or add.sym.id != PrimIDs.ADD or not all(isinstance(t, TensorProxy) for t in add.args):
+                    return None
+                if self._resolve(add.args[1].name) != c_da.output.name:
+                    return None
+                c_in = prod.get(self._resolve(add.args[0].name))
+                if c_in is None or c_in.sym.id != PrimIDs.CONVERT_ELEMENT_TYPE or self._single_consumer(c_in.output.name, consumers, region_outs) is not add:
+                    return None
+                cast = self._single_consumer(add.output.name, consumers, region_outs)
+                if cast is None or cast.sym.id != PrimIDs.CONVERT_ELEMENT_TYPE or cast.output.dtype != da.dtype:
+                    return None
+                other, out = c_in.args[0], cast.output
+                chain = [c_da, add, c_in, cast]
+            else:
+                add = self._single_consumer(da.name, consumers, region_outs)
+                if add is None or add.sym.id != PrimIDs.ADD or not all(isinstance(t, TensorProxy) for t in add.args):
+                    return None
+                if self._resolve(add.args[1].name) != da.name:
+                    return None
+                other, out = add.args[0], add.output
+                chain = [add]
+            if not isinstance(other, TensorProxy) or tuple(other.shape) != tuple(da.shape) or other.dtype != da.dtype:
+                return None
+            on = self._resolve(other.name)
+            # dh_in must not itself depend on this norm's outputs
+            if self._depends_on(on, {da.name, dw.name if dw is not None else ""}, prod):
+                return None
+            names = (self._resolve(dy.name), self._resolve(a.name), self._resolve(weight.name) if weight is not None else None,
+                     self._resolve(rstd.name), on, out.name, dw.name if dw is not None else None)
+
+            def run(env):
+                dyn, an, wn, rsn, on_, outn, dwn = names
+                dx, dwv = ops.rmsnorm_bwd(env[dyn], env[an], env[wn] if wn else None, env[rsn], env[on_])
+                env[outn] = dx
+                if dwn is not None:
+                    env[dwn] = dwv
+
+            absorbed.update(id(c) for c in chain)
+            ins = [n for n in names[:5] if n]
+            return _Step("b200_rms_norm_bwd+residual", run), ins, [n for n in (out.name, names[6]) if n]
+        return None
+
+    def _depends_on(self, name: str, targets: set, prod) -> bool:
+        seen, stack = set(), [name]
+        while stack:
+            n = stack.pop()
+            if n in targets:
+                return True
+            if n in seen:
+                continue
+            seen.add(n)
+            b = prod.get(n)
+            if b is not None:
+                stack.extend(self._arg_names(b))
+        return False
+
+    # ---- pointwise waves -----------------------------------------------------------------------------------
+    def _lower_wave(self, wave: list[BoundSymbol], needed: set) -> list[_Step]:
+        # connected components over values produced inside the wave
+        parent: dict[int, int] = {id(b): id(b) for b in wave}
+
+        def find(x):
+            while parent[x] != x:
+                parent[x] = parent[parent[x]]
+                x = parent[x]
+            return x
+
+        owner = {o.name: id(b) for b in wave for o in _outs_of(b)}
+        for b in wave:
+            for n in self._arg_names(b):
+                if n in owner:
+                    parent[find(id(b))] = find(owner[n])
+        comps: dict[int, list[BoundSymbol]] = {}
+        for b in wave:
+            comps.setdefault(find(id(b)), []).append(b)
+        steps: list[_Step] = []
+        for comp in comps.values():
+            steps.extend(self._lower_component(comp, needed))
+        return steps
+
+    def _lower_component(self, comp: list[BoundSymbol], needed: set) -> list[_Step]:
+        produced = {o.name for b in comp for o in _outs_of(b)}
+        outs = [o.name for b in comp for o in _outs_of(b) if o.name in needed]
+        if not outs:
+            return []
+        inputs: dict[str, tuple] = {}
+        nodes: list[PwNode] = []
+        r = lambda a: self._resolve(a.name) if isinstance(a, Proxy) else a
+        for b in comp:
+            opname = _PW_OPNAME[b.sym.id]
+            out = b.output
+            for a in b.flat_proxy_args:
+                n = self._resolve(a.name)
+                if n not in produced and n not in inputs:
+                    inputs[n] = (_tdtype(a.dtype), tuple(a.shape))
+            if opname == "broadcast_in_dim":
+                a, shape, bdims = b.args
+                nodes.append(PwNode("broadcast_in_dim", out.name, _tdtype(out.dtype), tuple(out.shape), (r(a), tuple(bdims))))
+            elif opname == "convert":
+                nodes.append(PwNode("convert", out.name, _tdtype(out.dtype), tuple(out.shape), (r(b.args[0]),)))
+            else:
+                nodes.append(PwNode(opname, out.name, _tdtype(out.dtype), tuple(out.shape), tuple(r(a) for a in b.args)))
+        try:
+            specs = compile_region(inputs, nodes, outs)
+        except PwUnsupported:
+            if len(comp) == 1:
+                raise
+            # too large for one program (registers / code words / operands): cut the chain in two
+            mid = len(comp) // 2
+            first, second = comp[:mid], comp[mid:]
+            needed_mid = set(needed)
+            for b in second:
+                needed_mid.update(self._arg_names(b))
+            return self._lower_component(first, needed_mid) + self._lower_component(second, needed)
+        steps = []
+        for spec in specs:
+            native = _native_for(spec)
+            if native is not None:
+                steps.append(native)
+                continue
+            launch = PwLaunch(spec)
+
+            def run(env, launch=launch):
+                env.update(launch.run(env))
+
+            steps.append(_Step("b200k_pointwise", run))
+        return steps
+
+    # ---- call ---------------------------------------------------------------------------------------------------
+    def __call__(self, *args):
+        env = dict(zip(self.input_names, args))
+        for s in self.steps:
+            s.run(env)
+        return tuple(env[self._resolve(n)] for n in self.output_names)
+
+
+# Canonical signatures of pointwise programs that have a hand-written kernel (generated by
+# tools/gen_signatures.py from traces of the family's defining PyTorch expression; a CPU test regenerates them
+# and fails on drift).  signature -> (family, leaf roles in program order, output roles in program order)
+from ._signatures import NATIVE_SIGNATURES as _NATIVE_SIGNATURES  # noqa: E402
+
+
+def _native_for(spec) -> _Step | None:
+    entry = _NATIVE_SIGNATURES.get(spec.signature)
+    if entry is None:
+        return None
+    kind, leaf_roles, out_roles = entry
+    role_in = {role: name for role, (name, _) in zip(leaf_roles, spec.leaves)}
+    role_out = {role: name for role, (name, _, _) in zip(out_roles, spec.outputs)}
+    shape = spec.iter_shape
+    if kind == "swiglu_fwd":
+
+        def run(env):
+            env[role_out["out"]] = ops.swiglu_fwd(env[role_in["a"]], env[role_in["b"]]).view(shape)
+
+        return _Step("b200k_swiglu_fwd", run)
+    if kind == "swiglu_bwd":
+
+        def run(env):
+            da, db = ops.swiglu_bwd(env[role_in["a"]], env[role_in["b"]], env[role_in["g"]])
+            env[role_out["da"]], env[role_out["db"]] = da.view(shape), db.view(shape)
+
+        return _Step("b200k_swiglu_bwd", run)
+    return None

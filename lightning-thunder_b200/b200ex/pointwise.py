@@ -1,0 +1,365 @@
+"""Compiler and launcher for generic pointwise regions (the b200k_pointwise entry point).
+
+A fused region that contains only elementwise prims, ``convert_element_type`` and
+``broadcast_in_dim`` is described by a small neutral IR (:class:`PwNode`); :func:`compile_region`
+turns it into one register program per distinct output shape, :class:`PwLaunch` binds runtime
+tensors (any strides; broadcasts become zero strides) and calls the C-ABI.  This is the generic
+counterpart of nvFuser's pointwise scheduler behind ``FusionDefinitionWrapper.__call__``
+(thunder/executors/nvfuserex_impl.py:526-576); it knows nothing about thunder itself, the executor
+(b200ex/executor.py) translates bound symbols into the IR.
+
+Numerics: every value is fp32 inside the program.  A node whose result dtype is bf16/f16 gets an
+explicit rounding instruction, which reproduces the reference's torch-executor behaviour of computing
+each op in fp32 and storing the declared dtype (thunder/executors/torchex.py:80-87).
+"""
+
+from __future__ import annotations
+
+import ctypes
+import hashlib
+import itertools
+import struct
+from dataclasses import dataclass, field
+
+import torch
+
+from . import _lib
+
+MAX_IN, MAX_OUT, MAX_REG, MAX_CODE = 10, 6, 48, 192
+
+OPS = [
+    "const", "mov", "add", "sub", "mul", "div", "neg", "abs", "exp", "log", "sqrt", "rsqrt", "reciprocal", "erf", "tanh", "pow",
+    "maximum", "minimum", "gt", "ge", "lt", "le", "eq", "ne", "where", "rnd_bf16", "rnd_f16", "and", "or", "not", "sign",
+    "floor", "ceil", "exp2", "log2", "log1p", "expm1", "sin", "cos", "erfc", "sigmoid", "trunc", "round",
+]
+OPCODE = {n: i for i, n in enumerate(OPS)}
+BINARY = {"add", "sub", "mul", "div", "pow", "maximum", "minimum", "gt", "ge", "lt", "le", "eq", "ne", "and", "or"}
+UNARY = {"neg", "abs", "exp", "log", "sqrt", "rsqrt", "reciprocal", "erf", "tanh", "not", "sign", "floor", "ceil", "exp2", "log2",
+         "log1p", "expm1", "sin", "cos", "erfc", "sigmoid", "trunc", "round"}
+# ops whose fp32 result is exactly representable whenever the operands are: no rounding instruction needed
+EXACT = {"neg", "abs", "where", "mov", "maximum", "minimum", "sign", "gt", "ge", "lt", "le", "eq", "ne", "and", "or", "not",
+         "floor", "ceil", "trunc", "round"}
+COMPARE = {"gt", "ge", "lt", "le", "eq", "ne", "and", "or", "not"}
+
+DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2, torch.bool: 3}
+
+
+class PwUnsupported(Exception):
+    """The region cannot be expressed as a b200k_pointwise program (the executor then declines it)."""
+
+
+@dataclass(frozen=True)
+class PwNode:
+    op: str  # an entry of OPS, or "convert" / "broadcast_in_dim"
+    out: str
+    dtype: torch.dtype
+    shape: tuple
+    args: tuple  # value names (str) or Python numbers; broadcast_in_dim: (a, broadcast_dims)
+
+
+@dataclass
+class PwProgramSpec:
+    iter_shape: tuple
+    leaves: list  # [(input name, mapping)]  mapping[i] = iteration dim of the input's dim i
+    code: list  # uint32 words
+    n_reg: int
+    outputs: list  # [(name, dtype, register)]
+    signature: str = ""  # canonical text of the program (used to route known families to native kernels)
+
+
+class _Operand(ctypes.Structure):
+    _fields_ = [("ptr", ctypes.c_void_p), ("s0", ctypes.c_int64), ("s1", ctypes.c_int64), ("inner", ctypes.c_int32), ("dtype", ctypes.c_int32)]
+
+
+class _Program(ctypes.Structure):
+    _fields_ = [
+        ("d0", ctypes.c_int64), ("d1", ctypes.c_int64), ("d2", ctypes.c_int64),
+        ("n_in", ctypes.c_int32), ("n_out", ctypes.c_int32), ("n_code", ctypes.c_int32), ("n_reg", ctypes.c_int32),
+        ("inp", _Operand * MAX_IN), ("out", _Operand * MAX_OUT), ("out_reg", ctypes.c_int32 * MAX_OUT), ("code", ctypes.c_uint32 * MAX_CODE),
+    ]
+
+
+def _f32_bits(x: float) -> int:
+    x = float(x)
+    try:
+        return struct.unpack("<I", struct.pack("<f", x))[0]
+    except OverflowError:  # |x| beyond fp32 range rounds to infinity, as a float32 cast would
+        return 0x7F800000 if x > 0 else 0xFF800000
+
+
+# --------------------------------------------------------------------------------------------------
+# Compilation
+# --------------------------------------------------------------------------------------------------
+def compile_region(inputs: dict, nodes: list, outputs: list) -> list:
+    """inputs: name -> (dtype, shape); nodes in execution order; outputs: value names.
+    Returns one :class:`PwProgramSpec` per distinct output shape.  Raises :class:`PwUnsupported`."""
+    producer = {n.out: n for n in nodes}
+    meta = {k: v for k, v in inputs.items()}
+    for n in nodes:
+        meta[n.out] = (n.dtype, tuple(n.shape))
+    for name, (dt, _) in meta.items():
+        if dt not in DTYPE_CODE:
+            raise PwUnsupported(f"dtype {dt} of {name}")
+    groups: dict[tuple, list] = {}
+    for o in outputs:
+        if o not in meta:
+            raise PwUnsupported(f"unknown output {o}")
+        groups.setdefault(tuple(meta[o][1]), []).append(o)
+    specs = []
+    for shape, outs in groups.items():
+        # canonical output order: the permutation with the smallest signature (programs with up to 3 outputs),
+        # so that the same dataflow always yields the same signature regardless of proxy naming
+        best = None
+        perms = itertools.permutations(outs) if len(outs) <= 3 else [tuple(outs)]
+        for perm in perms:
+            spec = _compile_group(shape, list(perm), inputs, producer, meta)
+            if best is None or spec.signature < best.signature:
+                best = spec
+        specs.append(best)
+    return specs
+
+
+def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
+    ssa = []  # (op, a, b, c, imm)  operands are ssa ids
+    memo: dict = {}
+    leaves: list = []
+    leaf_ids: dict = {}
+    consts: dict = {}
+
+    def emit(op, a=-1, b=-1, c=-1, imm=None):
+        ssa.append((op, a, b, c, imm))
+        return len(ssa) - 1
+
+    def const(x):
+        key = _f32_bits(x)
+        if key not in consts:
+            consts[key] = emit("const", imm=key)
+        return consts[key]
+
+    def value(name, mapping):
+        key = (name, mapping)
+        if key in memo:
+            return memo[key]
+        if name in inputs:
+            if key not in leaf_ids:
+                leaf_ids[key] = emit("leaf", imm=len(leaves))
+                leaves.append((name, mapping))
+            memo[key] = leaf_ids[key]
+            return memo[key]
+        n = producer.get(name)
+        if n is None:
+            raise PwUnsupported(f"value {name} has no producer in the region")
+        memo[key] = r = node(n, mapping)
+        return r
+
+    def arg(a, mapping):
+        if isinstance(a, str):
+            return value(a, mapping)
+        if isinstance(a, (bool, int, float)):
+            return const(float(a))
+        raise PwUnsupported(f"operand {a!r}")
+
+    def rounded(r, n):
+        if n.op in EXACT:
+            return r
+        if n.dtype == torch.bfloat16:
+            return emit("rnd_bf16", r)
+        if n.dtype == torch.float16:
+            return emit("rnd_f16", r)
+        return r
+
+    def node(n: PwNode, mapping):
+        if n.op == "broadcast_in_dim":
+            a, bdims = n.args
+            return value(a, tuple(mapping[d] for d in bdims))
+        if n.op == "convert":
+            r = arg(n.args[0], mapping)
+            src_dt = meta[n.args[0]][0] if isinstance(n.args[0], str) else torch.float32
+            if n.dtype == torch.bfloat16 and src_dt != torch.bfloat16:
+                return emit("rnd_bf16", r)
+            if n.dtype == torch.float16 and src_dt != torch.float16:
+                return emit("rnd_f16", r)
+            if n.dtype == torch.bool and src_dt != torch.bool:
+                return emit("ne", r, const(0.0))
+            return r
+        if n.op == "mov":
+            return arg(n.args[0], mapping)
+        if n.op == "where":
+            c, a, b = (arg(x, mapping) for x in n.args)
+            return emit("where", c, a, b)
+        if n.op == "pow" and isinstance(n.args[1], (int, float)) and not isinstance(n.args[1], bool):
+            # ATen evaluates small constant exponents by multiplication / sqrt (pow_tensor_scalar_optimized_kernel)
+            a, e = arg(n.args[0], mapping), float(n.args[1])
+            if e == 2.0:
+                return rounded(emit("mul", a, a), n)
+            if e == 3.0:
+                return rounded(emit("mul", emit("mul", a, a), a), n)
+            if e == 0.5:
+                return rounded(emit("sqrt", a), n)
+            if e == -0.5:
+                return rounded(emit("rsqrt", a), n)
+            if e == -1.0:
+                return rounded(emit("reciprocal", a), n)
+            if e == 1.0:
+                return a
+            return rounded(emit("pow", a, const(e)), n)
+        if n.op in BINARY:
+            a, b = arg(n.args[0], mapping), arg(n.args[1], mapping)
+            return rounded(emit(n.op, a, b), n)
+        if n.op in UNARY:
+            return rounded(emit(n.op, arg(n.args[0], mapping)), n)
+        raise PwUnsupported(f"op {n.op}")
+
+    ident = tuple(range(len(iter_shape)))
+    out_ids = [value(o, ident) for o in outs]
+
+    # canonical signature: the SSA text with leaves numbered in first-use order (input names erased)
+    sig = ";".join(f"{op}({a},{b},{c},{imm if op != 'leaf' else ''})" for op, a, b, c, imm in ssa)
+    sig += "|" + ",".join(f"{oid}:{meta[o][0]}" for oid, o in zip(out_ids, outs))
+    # leaf layout relative to the iteration space, rank independent: "*" = spans every dim, else the dims it
+    # covers counted from the innermost one
+    nd = len(iter_shape)
+    sig += "|" + ",".join(f"{meta[nm][0]}:" + ("*" if tuple(mp) == ident else "/".join(str(d - nd) for d in mp)) for nm, mp in leaves)
+
+    # register allocation: leaves are preloaded into registers 0..n_in-1, everything else linear scan
+    if len(leaves) > MAX_IN or len(outs) > MAX_OUT:
+        raise PwUnsupported("too many operands for one pointwise program")
+    last_use = {}
+    for i, (op, a, b, c, _) in enumerate(ssa):
+        for x in (a, b, c):
+            if x >= 0:
+                last_use[x] = i
+    for oid in out_ids:
+        last_use[oid] = len(ssa)
+    reg_of, free, n_reg = {}, [], len(leaves)
+    code: list = []
+    for i, (op, a, b, c, imm) in enumerate(ssa):
+        if op == "leaf":
+            reg_of[i] = imm
+        srcs = [reg_of[x] for x in (a, b, c) if x >= 0]
+        # operands dying here can be reused for the destination (reads happen before the write per element)
+        for x in {a, b, c}:
+            if x >= 0 and last_use.get(x) == i and x not in out_ids:
+                free.append(reg_of[x])
+        if op == "leaf":
+            continue
+        if i not in last_use:
+            # dead value (can happen through memoised broadcasts); still needs a scratch destination
+            pass
+        if free:
+            dst = free.pop()
+        else:
+            dst = n_reg
+            n_reg += 1
+        reg_of[i] = dst
+        if n_reg > MAX_REG:
+            raise PwUnsupported("pointwise program needs too many registers")
+        if op == "const":
+            code += [OPCODE["const"] | dst << 8, imm]
+        elif op == "where":
+            code += [OPCODE["where"] | dst << 8 | srcs[0] << 16 | srcs[1] << 24, srcs[2]]
+        elif op in BINARY:
+            code.append(OPCODE[op] | dst << 8 | srcs[0] << 16 | srcs[1] << 24)
+        else:
+            code.append(OPCODE[op] | dst << 8 | srcs[0] << 16)
+    if len(code) > MAX_CODE:
+        raise PwUnsupported("pointwise program too long")
+    # two outputs may not share a register with a later-written value: outputs were excluded from reuse above
+    outputs = [(o, meta[o][0], reg_of[oid]) for o, oid in zip(outs, out_ids)]
+    return PwProgramSpec(tuple(iter_shape), leaves, code, max(n_reg, 1), outputs, hashlib.sha1(sig.encode()).hexdigest())
+
+
+# --------------------------------------------------------------------------------------------------
+# Launch
+# --------------------------------------------------------------------------------------------------
+def _collapse(shape, strides_list):
+    """Merge adjacent iteration dims that every operand traverses contiguously (or broadcasts in both).
+    Returns (shape, strides_list) with size-1 dims dropped."""
+    dims = [d for d in range(len(shape)) if shape[d] != 1]
+    if not dims:
+        return [1], [[0] for _ in strides_list]
+    out_shape = [shape[dims[0]]]
+    out_strides = [[s[dims[0]]] for s in strides_list]
+    for d in dims[1:]:
+        n = shape[d]
+        if all(os[-1] == s[d] * n for os, s in zip(out_strides, strides_list)):
+            out_shape[-1] *= n
+            for os, s in zip(out_strides, strides_list):
+                os[-1] = s[d]
+        else:
+            out_shape.append(n)
+            for os, s in zip(out_strides, strides_list):
+                os.append(s[d])
+    return out_shape, out_strides
+
+
+class PwLaunch:
+    """A compiled program bound to its region: ``run(env)`` reads input tensors from ``env`` by name and
+    returns {output name: new contiguous tensor}."""
+
+    def __init__(self, spec: PwProgramSpec):
+        self.spec = spec
+
+    def _leaf_strides(self, t: torch.Tensor, mapping, ndim):
+        st = [0] * ndim
+        for i, d in enumerate(mapping):
+            if t.shape[i] != 1:
+                st[d] = t.stride(i)
+        return st
+
+    def run(self, env: dict) -> dict:
+        spec = self.spec
+        shape = list(spec.iter_shape)
+        nd = len(shape)
+        tensors = []
+        for name, mapping in spec.leaves:
+            t = env[name]
+            if not isinstance(t, torch.Tensor) or not t.is_cuda:
+                raise RuntimeError(f"b200ex pointwise: operand {name} is not a CUDA tensor")
+            if t.dim() != len(mapping):
+                raise RuntimeError(f"b200ex pointwise: operand {name} has rank {t.dim()}, expected {len(mapping)}")
+            tensors.append(t)
+        dev = tensors[0].device if tensors else torch.device("cuda", torch.cuda.current_device())
+        outs = {name: torch.empty(shape, dtype=dt, device=dev) for name, dt, _ in spec.outputs}
+        numel = 1
+        for n in shape:
+            numel *= n
+        if numel == 0:
+            return outs
+        in_strides = [self._leaf_strides(t, m, nd) for t, (_, m) in zip(tensors, spec.leaves)]
+        contig = [0] * nd
+        acc = 1
+        for d in range(nd - 1, -1, -1):
+            contig[d] = acc
+            acc *= shape[d]
+        cshape, cstrides = _collapse(shape, in_strides + [contig])
+        if len(cshape) > 3:
+            # more than three independent strides: give every operand the contiguous broadcast layout first
+            # (a strided copy by torch; rare — needs e.g. several differently permuted inputs)
+            fixed = []
+            for t, (_, m) in zip(tensors, spec.leaves):
+                full = [1] * nd
+                for i, d in enumerate(m):
+                    full[d] = t.shape[i]
+                fixed.append(t.reshape(full).expand(shape).contiguous())
+            tensors = fixed
+            cshape, cstrides = _collapse(shape, [list(contig) for _ in tensors] + [contig])
+        while len(cshape) < 3:
+            cshape.insert(0, 1)
+            for s in cstrides:
+                s.insert(0, 0)
+        P = _Program()
+        P.d0, P.d1, P.d2 = cshape
+        P.n_in, P.n_out, P.n_code, P.n_reg = len(tensors), len(spec.outputs), len(spec.code), spec.n_reg
+        for k, (t, s) in enumerate(zip(tensors, cstrides[:-1])):
+            P.inp[k] = _Operand(t.data_ptr(), s[0], s[1], s[2], DTYPE_CODE[t.dtype])
+        so = cstrides[-1]
+        for k, (name, dt, reg) in enumerate(spec.outputs):
+            P.out[k] = _Operand(outs[name].data_ptr(), so[0], so[1], so[2], DTYPE_CODE[dt])
+            P.out_reg[k] = reg
+        for k, w in enumerate(spec.code):
+            P.code[k] = w
+        with torch.cuda.device(dev):
+            rc = _lib.lib().b200k_pointwise(ctypes.byref(P), torch.cuda.current_stream(dev).cuda_stream)
+        _lib.check(rc, "b200k_pointwise")
+        return outs
