@@ -43,6 +43,7 @@ EXPORTS: dict[str, tuple] = {
     "b200k_bias_act_fwd": (c_int, [c_void_p] * 3 + [c_int64, c_int64, c_int, c_int, c_void_p]),
     "b200k_bias_act_bwd_scratch_bytes": (c_int64, [c_int64, c_int64]),
     "b200k_bias_act_bwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_int64, c_int, c_int, c_void_p]),
+    "b200k_pointwise": (c_int, [c_void_p, c_void_p]),
 }
 
 ABI_VERSION = 1

@@ -47,7 +47,7 @@ from thunder.executors.utils import Region
 from thunder.extend import FUEL_LEVEL, FusionExecutor, register_executor
 
 from . import ops
-from .pointwise import PwLaunch, PwNode, PwUnsupported, compile_region
+from .pointwise import PwLaunch, PwNode, PwUnsupported, compile_chain
 
 __all__ = ["ex", "B200Executor", "qkv_split_rope", "swiglu"]
 
@@ -872,18 +872,7 @@ class B200Region:
                 nodes.append(PwNode("convert", out.name, _tdtype(out.dtype), tuple(out.shape), (r(b.args[0]),)))
             else:
                 nodes.append(PwNode(opname, out.name, _tdtype(out.dtype), tuple(out.shape), tuple(r(a) for a in b.args)))
-        try:
-            specs = compile_region(inputs, nodes, outs)
-        except PwUnsupported:
-            if len(comp) == 1:
-                raise
-            # too large for one program (registers / code words / operands): cut the chain in two
-            mid = len(comp) // 2
-            first, second = comp[:mid], comp[mid:]
-            needed_mid = set(needed)
-            for b in second:
-                needed_mid.update(self._arg_names(b))
-            return self._lower_component(first, needed_mid) + self._lower_component(second, needed)
+        specs = compile_chain(inputs, nodes, outs)  # PwUnsupported propagates: the fusion pass then declines the region
         steps = []
         for spec in specs:
             native = _native_for(spec)

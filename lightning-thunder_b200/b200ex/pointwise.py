@@ -119,6 +119,34 @@ def compile_region(inputs: dict, nodes: list, outputs: list) -> list:
     return specs
 
 
+def compile_chain(inputs: dict, nodes: list, outputs: list) -> list:
+    """Like :func:`compile_region`, but a region too large for one program (registers, code words, operand
+    slots) is cut into consecutive programs that hand intermediates over through memory.  The returned
+    specs must be launched in order."""
+    try:
+        return compile_region(inputs, nodes, outputs)
+    except PwUnsupported:
+        if len(nodes) <= 1:
+            raise
+    mid = len(nodes) // 2
+    first, second = nodes[:mid], nodes[mid:]
+    made_first = {n.out for n in first}
+    made_second = {n.out for n in second}
+    used_by_second = set()
+    for n in second:
+        args = n.args[:1] if n.op == "broadcast_in_dim" else n.args
+        used_by_second.update(a for a in args if isinstance(a, str))
+    outs_first = [n.out for n in first if n.out in used_by_second or n.out in outputs]
+    meta_first = {n.out: (n.dtype, tuple(n.shape)) for n in first}
+    inputs_second = dict(inputs)
+    inputs_second.update({o: meta_first[o] for o in outs_first})
+    outs_second = [o for o in outputs if o in made_second]
+    specs = compile_chain(inputs, first, outs_first) if outs_first else []
+    if outs_second:
+        specs += compile_chain(inputs_second, second, outs_second)
+    return specs
+
+
 def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
     ssa = []  # (op, a, b, c, imm)  operands are ssa ids
     memo: dict = {}
@@ -353,7 +381,7 @@ class PwLaunch:
         P.n_in, P.n_out, P.n_code, P.n_reg = len(tensors), len(spec.outputs), len(spec.code), spec.n_reg
         for k, (t, s) in enumerate(zip(tensors, cstrides[:-1])):
             P.inp[k] = _Operand(t.data_ptr(), s[0], s[1], s[2], DTYPE_CODE[t.dtype])
-        so = cstrides[-1]
+        so = [cshape[1] * cshape[2], cshape[2], 1]  # outputs are freshly allocated, contiguous over the collapsed box
         for k, (name, dt, reg) in enumerate(spec.outputs):
             P.out[k] = _Operand(outs[name].data_ptr(), so[0], so[1], so[2], DTYPE_CODE[dt])
             P.out_reg[k] = reg

@@ -1,0 +1,165 @@
+"""GPU: ``thunder.jit(fn, executors=[b200])`` against ``thunder.jit(fn, executors=["torch"])`` — the reference's
+torch-executor output on the same inputs is the parity target BASELINE.json names — forward and backward,
+for every fused-region family and for a small Llama-style model."""
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from parity import TOL, assert_parity
+from thunder_env import fusions, import_thunder
+
+pytestmark = pytest.mark.gpu
+
+try:
+    thunder, b200 = import_thunder()
+except ImportError as e:  # pragma: no cover
+    pytest.skip(f"reference not importable: {e}", allow_module_level=True)
+
+DEV = "cuda:0"
+BF, F32 = torch.bfloat16, torch.float32
+
+
+def _both(fn, args, cot_seed=0, opts=None):
+    """Run fn under b200 and under the torch executor on clones of args; return (outs, grads) for both."""
+    res = []
+    for execs in ([b200.ex], ["torch"]):
+        a = [t.detach().clone().requires_grad_(t.is_floating_point() and t.requires_grad) if isinstance(t, torch.Tensor) else t for t in args]
+        jf = thunder.jit(fn, executors=execs, **(opts or {}))
+        out = jf(*a)
+        outs = list(out) if isinstance(out, (tuple, list)) else [out]
+        g = torch.Generator(device=DEV).manual_seed(cot_seed)
+        cots = [torch.randn(o.shape, generator=g, device=DEV, dtype=torch.float32).to(o.dtype) for o in outs]
+        diff = [t for t in a if isinstance(t, torch.Tensor) and t.requires_grad]
+        grads = torch.autograd.grad(outs, diff, grad_outputs=cots, allow_unused=True) if diff else []
+        res.append((outs, list(grads), jf))
+    torch.cuda.synchronize()
+    return res
+
+
+def _mk(*shape, dtype=BF, grad=True, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed + sum(shape))
+    return (torch.randn(*shape, generator=g) * scale).to(dtype).to(DEV).requires_grad_(grad)
+
+
+def _compare(res, what, ulp=None, grad_atol=0.0):
+    (o1, g1, _), (o2, g2, _) = res
+    for i, (a, b) in enumerate(zip(o1, o2)):
+        assert_parity(a, b, what=f"{what} out[{i}]", ulp_scale=ulp(b) if ulp else None)
+    for i, (a, b) in enumerate(zip(g1, g2)):
+        if a is None and b is None:
+            continue
+        assert_parity(a, b, what=f"{what} grad[{i}]", ulp_scale=ulp(b) if ulp else None, atol_extra=grad_atol)
+
+
+@pytest.mark.parametrize("dtype", [BF, F32])
+def test_rmsnorm_residual(dtype):
+    def f(x, r, w):
+        h = x + r
+        return h, F.rms_norm(h, (512,), w, 1e-5)
+
+    res = _both(f, [_mk(64, 512, dtype=dtype, seed=1), _mk(64, 512, dtype=dtype, seed=2), _mk(512, dtype=dtype, seed=3)])
+    kinds = [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
+    assert "b200_rms_norm_fwd+residual" in kinds
+    # gradients of a sum of rounded terms: one bf16 ulp of the operands' magnitude
+    _compare(res, f"rmsnorm {dtype}", ulp=(lambda b: b.float().abs() + 4.0) if dtype is BF else None, grad_atol=0 if dtype is BF else 2e-5)
+
+
+def test_swiglu_inline_expression():
+    res = _both(lambda a, b: F.silu(a) * b, [_mk(128, 1024, seed=4, scale=2.0), _mk(128, 1024, seed=5)])
+    kinds = [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
+    assert kinds, "swiglu was not claimed"
+    _compare(res, "swiglu", ulp=lambda b: b.float().abs() * 2 + 1e-2)
+
+
+def test_swiglu_function_is_native():
+    res = _both(lambda a, b: b200.swiglu(a, b), [_mk(64, 2048, seed=6, scale=2.0), _mk(64, 2048, seed=7)])
+    fw = fusions(thunder.last_traces(res[0][2])[-1])
+    assert [k for _, ks in fw for k in ks] == ["b200_swiglu"]
+    _compare(res, "b200.swiglu", ulp=lambda b: b.float().abs() * 2 + 1e-2)
+
+
+@pytest.mark.parametrize("dtype", [BF, F32])
+def test_cross_entropy(dtype):
+    logits = _mk(256, 32064, dtype=dtype, seed=8, scale=2.0)
+    tgt = torch.randint(0, 32064, (256,), device=DEV)
+    tgt[5] = -100
+
+    def f(lg, t):
+        return F.cross_entropy(lg, t, ignore_index=-100)
+
+    res = _both(f, [logits, tgt])
+    assert "b200_cross_entropy_fwd" in [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
+    _compare(res, f"cross_entropy {dtype}", ulp=(lambda b: b.float().abs() * 16 + 1e-7) if dtype is BF else None)
+
+
+def test_qkv_split_rope_function():
+    qkv = _mk(2, 64, (8 + 4) * 32, seed=9)
+    cos, sin = _mk(64, 32, grad=False, seed=10), _mk(64, 32, grad=False, seed=11)
+    res = _both(lambda q, c, s: b200.qkv_split_rope(q, c, s, 8, 2, 32, 32), [qkv, cos, sin])
+    assert [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks] == ["b200_qkv_split_rope"]
+    _compare(res, "qkv_split_rope", grad_atol=2.0**-6)
+
+
+def test_bias_gelu_goes_through_the_generic_interpreter():
+    res = _both(lambda x, b: F.gelu(x + b), [_mk(256, 768, seed=12, scale=1.5), _mk(768, seed=13)])
+    assert "b200k_pointwise" in [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
+    _compare(res, "bias_gelu", ulp=lambda b: b.float().abs() * 4 + 2.0)
+
+
+def test_generic_pointwise_fp32_with_broadcasts():
+    def f(x, y, s):
+        z = torch.tanh(x) * y + torch.exp(-x * x) / (1.0 + y * y)
+        return torch.where(z > 0.1, z, 0.01 * z) * s, torch.sqrt(torch.abs(x)) + s
+
+    res = _both(f, [_mk(8, 33, 65, dtype=F32, seed=14), _mk(8, 33, 65, dtype=F32, seed=15), _mk(65, dtype=F32, seed=16)])
+    _compare(res, "generic pointwise", grad_atol=1e-5)
+
+
+def test_region_callable_is_reused_and_handles_new_strides():
+    jf = thunder.jit(lambda a, b: F.silu(a) * b, executors=[b200.ex])
+    a, b = _mk(64, 256, grad=False, seed=17), _mk(64, 256, grad=False, seed=18)
+    ref = F.silu(a) * b
+    out1 = jf(a, b)
+    at = a.t().contiguous().t()  # same shape, column-major strides
+    out2 = jf(at, b)
+    assert_parity(out1, ref, what="contiguous", ulp_scale=ref.float().abs())
+    assert_parity(out2, ref, what="transposed strides", ulp_scale=ref.float().abs())
+    assert thunder.cache_misses(jf) == 1
+
+
+@pytest.mark.parametrize("fusion_type", ["consecutive", "dataflow"])
+def test_tiny_llama_forward_backward(fusion_type):
+    """A 2-layer Llama-style GPT (RMSNorm, fused-QKV RoPE with GQA, SwiGLU, cross-entropy inside the jitted callable):
+    loss and every parameter gradient against the torch executor."""
+    from baseline.llama_model import GPT, build_rope_cache, tiny_config
+    from thunder.executors.sdpaex import sdpa_ex
+
+    cfg = tiny_config(n_embd=128, intermediate_size=256, n_head=4, n_query_groups=2, padded_vocab_size=512)
+    torch.manual_seed(0)
+    model = GPT(cfg).to(DEV).to(BF)
+    B, T = 2, 64
+    cos, sin = build_rope_cache(T, cfg.rope_n_elem, device=DEV, dtype=BF)
+    idx = torch.randint(0, cfg.padded_vocab_size, (B, T), device=DEV)
+    tgt = torch.randint(0, cfg.padded_vocab_size, (B, T), device=DEV)
+    tgt[0, :5] = -1
+    results = {}
+    for name, execs in (("b200", [sdpa_ex, b200.ex]), ("torch", [sdpa_ex, "torch"])):
+        model.zero_grad(set_to_none=True)
+        jm = thunder.jit(model, executors=execs, fusion_type=fusion_type)
+        loss = jm(idx, cos, sin, tgt)
+        loss.backward()
+        results[name] = (loss.detach().clone(), {n: p.grad.detach().clone() for n, p in model.named_parameters()}, jm)
+    torch.cuda.synchronize()
+    jm = results["b200"][2]
+    fk = [k for _, ks in fusions(thunder.last_traces(jm)[-1]) for k in ks]
+    bk = [k for _, ks in fusions(thunder.last_backward_traces(jm)[-1]) for k in ks]
+    assert fk.count("b200_qkv_split_rope") == cfg.n_layer and "b200_cross_entropy_fwd" in fk and "b200_cross_entropy_bwd" in bk
+    assert fk.count("b200_rms_norm_fwd+residual") == 2 * cfg.n_layer
+    torch.testing.assert_close(results["b200"][0].float(), results["torch"][0].float(), rtol=1.6e-2, atol=1e-5)
+    for n, g in results["b200"][1].items():
+        ref = results["torch"][1][n]
+        # parameter gradients are GEMM outputs of bf16 activations that differ by an ulp here and there: compare
+        # in the aggregate, relative to the gradient's scale
+        err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
+        assert err.item() < 2e-2, f"grad {n}: relative error {err.item():.3e}"

@@ -1,0 +1,91 @@
+"""CPU: the pointwise-program compiler (no thunder, no GPU): code generation, register allocation limits,
+rounding insertion and the canonical signature."""
+
+import pytest
+import torch
+
+from b200ex.pointwise import MAX_REG, OPCODE, PwNode, PwUnsupported, _collapse, compile_region
+
+BF, F32 = torch.bfloat16, torch.float32
+
+
+def _ops(spec):
+    out, i = [], 0
+    names = {v: k for k, v in OPCODE.items()}
+    while i < len(spec.code):
+        op = names[spec.code[i] & 0xFF]
+        out.append(op)
+        i += 2 if op in ("const", "where") else 1
+    return out
+
+
+def test_add_bf16_inserts_one_rounding():
+    nodes = [PwNode("convert", "xf", F32, (4, 8), ("x",)), PwNode("convert", "yf", F32, (4, 8), ("y",)),
+             PwNode("add", "s", F32, (4, 8), ("xf", "yf")), PwNode("convert", "o", BF, (4, 8), ("s",))]
+    (spec,) = compile_region({"x": (BF, (4, 8)), "y": (BF, (4, 8))}, nodes, ["o"])
+    assert _ops(spec) == ["add", "rnd_bf16"] and len(spec.leaves) == 2 and spec.iter_shape == (4, 8)
+
+
+def test_native_16bit_op_is_rounded_but_exact_ops_are_not():
+    nodes = [PwNode("exp", "e", BF, (8,), ("x",)), PwNode("neg", "n", BF, (8,), ("e",))]
+    (spec,) = compile_region({"x": (BF, (8,))}, nodes, ["n"])
+    assert _ops(spec) == ["exp", "rnd_bf16", "neg"]
+
+
+def test_broadcast_becomes_a_leaf_mapping_and_scalars_become_constants():
+    nodes = [PwNode("broadcast_in_dim", "bb", F32, (4, 8), ("b", (1,))), PwNode("add", "s", F32, (4, 8), ("x", "bb")),
+             PwNode("mul", "o", F32, (4, 8), ("s", 0.5))]
+    (spec,) = compile_region({"x": (F32, (4, 8)), "b": (F32, (8,))}, nodes, ["o"])
+    assert dict(spec.leaves) == {"x": (0, 1), "b": (1,)}
+    assert _ops(spec) == ["add", "const", "mul"]
+
+
+def test_pow_with_small_constant_exponent_is_strength_reduced():
+    (spec,) = compile_region({"x": (F32, (8,))}, [PwNode("pow", "o", F32, (8,), ("x", 3.0))], ["o"])
+    assert _ops(spec) == ["mul", "mul"]
+    (spec,) = compile_region({"x": (F32, (8,))}, [PwNode("pow", "o", F32, (8,), ("x", 2.5))], ["o"])
+    assert _ops(spec) == ["const", "pow"]
+
+
+def test_outputs_of_different_shape_get_separate_programs():
+    nodes = [PwNode("mul", "a", F32, (4, 1), ("r", 2.0)), PwNode("broadcast_in_dim", "ab", F32, (4, 8), ("a", (0, 1))),
+             PwNode("mul", "o", F32, (4, 8), ("x", "ab"))]
+    specs = compile_region({"r": (F32, (4, 1)), "x": (F32, (4, 8))}, nodes, ["a", "o"])
+    assert sorted(s.iter_shape for s in specs) == [(4, 1), (4, 8)]
+
+
+def test_signature_is_independent_of_names_rank_and_output_order():
+    def prog(names, shape, outs):
+        x, y, s, d = names
+        nodes = [PwNode("add", s, F32, shape, (x, y)), PwNode("sub", d, F32, shape, (x, y))]
+        return compile_region({x: (F32, shape), y: (F32, shape)}, nodes, outs)[0]
+
+    a = prog(("x", "y", "s", "d"), (4, 8), ["s", "d"])
+    b = prog(("p", "q", "t1", "t2"), (2, 3, 8), ["t2", "t1"])
+    assert a.signature == b.signature
+    c = compile_region({"x": (BF, (4, 8)), "y": (BF, (4, 8))}, [PwNode("add", "s", BF, (4, 8), ("x", "y"))], ["s"])[0]
+    assert c.signature != a.signature
+
+
+def test_unsupported_dtype_and_register_pressure():
+    with pytest.raises(PwUnsupported):
+        compile_region({"x": (torch.int64, (4,))}, [PwNode("add", "o", torch.int64, (4,), ("x", 1))], ["o"])
+    # a chain that keeps more than MAX_REG values alive
+    n = MAX_REG + 8
+    nodes = [PwNode("mul", f"m{i}", F32, (4,), ("x", float(i + 2))) for i in range(n)]
+    acc = "m0"
+    for i in range(1, n):
+        nodes.append(PwNode("add", f"a{i}", F32, (4,), (acc, f"m{i}")))
+        acc = f"a{i}"
+    outs = [f"m{i}" for i in range(0, n, 9)][:6]
+    with pytest.raises(PwUnsupported):
+        compile_region({"x": (F32, (4,))}, nodes, [acc] + [f"m{i}" for i in range(5)] + [f"m{i}" for i in range(5, 11)])
+
+
+def test_collapse_merges_contiguous_dims():
+    shape, strides = _collapse([2, 3, 4], [[12, 4, 1], [0, 0, 1], [12, 4, 1]])
+    assert shape == [6, 4] and strides == [[4, 1], [0, 1], [4, 1]]
+    shape, strides = _collapse([2, 3, 4], [[12, 4, 1], [12, 4, 1]])
+    assert shape == [24] and strides == [[1], [1]]
+    shape, strides = _collapse([1, 1], [[0, 0]])
+    assert shape == [1]
