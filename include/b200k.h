@@ -86,6 +86,32 @@ B200K_API int b200k_rmsnorm_bwd(const void* dy, const void* h, const void* weigh
                       int64_t rows, int64_t hidden, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * RMSNorm backward for callers that must not allocate.  (No counterpart in the reference: it exists for
+ * hosts of this library that cannot call cudaMalloc or any allocating routine at the point where the
+ * backward runs — a runtime that has handed all device memory to its own pool and forbids driver
+ * allocations, a real-time or signal-handling context, or a launch path that must stay allocation-free
+ * between two points of a stream.)
+ *
+ * Same computation, arguments and results as b200k_rmsnorm_bwd, except that the scratch for the dw partial
+ * rows is a fixed array of B200K_RMSNORM_BWD_NOALLOC_SCRATCH_BYTES inside the library's device image; every
+ * GPU that loads the library holds that much memory until the process exits.  The caller still passes all
+ * inputs and outputs.  The call itself performs no cudaMalloc / cudaFree and calls no allocating routine.
+ *
+ *  - Limit: returns B200K_ELIMIT ("size exceeds a documented maximum") when
+ *    b200k_rmsnorm_bwd_scratch_bytes(rows, hidden) exceeds the array (with weight != NULL).  On a 148-SM
+ *    B200 the array covers hidden <= 7084 elements for any number of rows, e.g. [8192 x 4096].
+ *  - First call on each device: resolves the array's device address (cudaGetSymbolAddress, with that
+ *    device current) and caches it.  Make that first call before starting any stream capture.
+ *  - The array is shared by all calls and keeps the previous call's contents.  Nothing in it has to start
+ *    at zero (every partial row is written before it is read), but two calls whose kernels can overlap on
+ *    the GPU — different streams without an ordering between them — race on it.  Serialise them.
+ * --------------------------------------------------------------------------------------------- */
+#define B200K_RMSNORM_BWD_NOALLOC_SCRATCH_BYTES (16u << 20)
+B200K_API int b200k_rmsnorm_bwd_noalloc(const void* dy, const void* h, const void* weight, const float* rstd,
+                                        const void* dh_in, void* dx, void* dw, int64_t rows, int64_t hidden,
+                                        int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * SwiGLU forward — SURVEY §8 row a7.  Replaces the region `silu(a) * b` built from ltorch.silu
  * (thunder/torch/__init__.py:2266 -> thunder/clang/__init__.py:1417) + ltorch.mul.
  *   u = round_T(a / (1 + exp(-a)));  out = round_T(f32(u) * f32(b))

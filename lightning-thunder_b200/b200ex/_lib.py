@@ -34,6 +34,7 @@ EXPORTS: dict[str, tuple] = {
     "b200k_rmsnorm_fwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_float, c_int, c_void_p]),
     "b200k_rmsnorm_bwd_scratch_bytes": (c_int64, [c_int64, c_int64]),
     "b200k_rmsnorm_bwd": (c_int, [c_void_p] * 8 + [c_int64, c_int64, c_int64, c_int, c_void_p]),
+    "b200k_rmsnorm_bwd_noalloc": (c_int, [c_void_p] * 7 + [c_int64, c_int64, c_int, c_void_p]),
     "b200k_swiglu_fwd": (c_int, [c_void_p] * 3 + [c_int64, c_int, c_void_p]),
     "b200k_swiglu_bwd": (c_int, [c_void_p] * 5 + [c_int64, c_int, c_void_p]),
     "b200k_cross_entropy_fwd": (c_int, [c_void_p] * 7 + [c_int64, c_int64, c_int64, c_int, c_int, c_void_p]),

@@ -8,6 +8,7 @@
 // the columns it owns across all rows the (persistent) CTA processes, writes one partial row per
 // CTA to scratch, and a second tiny kernel folds the partials (deterministic, no atomics).
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 #include "reduce.cuh"
@@ -794,4 +795,58 @@ extern "C" int b200k_rmsnorm_bwd(const void* dy, const void* h, const void* weig
         case B200K_F16: return dispatch_bwd<__half>(dy, h, weight, rstd, dh_in, dx, dw, scratch, scratch_bytes, rows, hidden, st);
         default: return B200K_EDTYPE;
     }
+}
+
+
+// -------------------------------------------------------------------------------------------
+// b200k_rmsnorm_bwd_noalloc: the same backward, for callers that cannot allocate device memory.
+//
+// The dw partial rows live in a fixed array inside this library's device image instead of a buffer the
+// caller provides.  The array's name is only a host-side handle: its device address is looked up once
+// per device with cudaGetSymbolAddress (with that device current) and cached; that pointer, never the
+// symbol itself, is what the kernels receive.
+// -------------------------------------------------------------------------------------------
+namespace {
+
+static __device__ __align__(256) unsigned char g_rmsnorm_bwd_static_scratch[B200K_RMSNORM_BWD_NOALLOC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+void* g_static_scratch_addr[kMaxDevices] = {};
+std::mutex g_static_scratch_mutex;
+
+// Device address of the static scratch array on the current device (resolved on first use per device).
+int static_scratch_address(void** out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (dev < 0 || dev >= kMaxDevices) return B200K_ELIMIT;
+    std::lock_guard<std::mutex> guard(g_static_scratch_mutex);
+    if (g_static_scratch_addr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_rmsnorm_bwd_static_scratch);
+        if (e != cudaSuccess) return static_cast<int>(e);
+        if (p == nullptr) return B200K_EINVAL;
+        g_static_scratch_addr[dev] = p;
+    }
+    *out = g_static_scratch_addr[dev];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int b200k_rmsnorm_bwd_noalloc(const void* dy, const void* h, const void* weight, const float* rstd, const void* dh_in,
+                                         void* dx, void* dw, int64_t rows, int64_t hidden, int dtype, void* stream) {
+    if (rows < 0 || hidden <= 0) return B200K_EINVAL;
+    // Reject shapes whose partial rows would not fit the fixed array before touching anything.
+    if (weight != nullptr && b200k_rmsnorm_bwd_scratch_bytes(rows, hidden) > static_cast<int64_t>(B200K_RMSNORM_BWD_NOALLOC_SCRATCH_BYTES))
+        return B200K_ELIMIT;
+    void* scratch = nullptr;
+    if (weight != nullptr && rows > 0) {
+        const int rc = static_scratch_address(&scratch);
+        if (rc != 0) return rc;
+    }
+    // Every partial row that the fold kernel reads is fully written by the producing grid first, so the
+    // array needs no clearing between calls even though it keeps the previous call's contents.
+    return b200k_rmsnorm_bwd(dy, h, weight, rstd, dh_in, dx, dw, scratch, static_cast<int64_t>(B200K_RMSNORM_BWD_NOALLOC_SCRATCH_BYTES),
+                             rows, hidden, dtype, stream);
 }
