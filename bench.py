@@ -514,11 +514,29 @@ def main():
     ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="rmsnorm", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="rmsnorm", choices=sorted(WORKLOADS) + ["llama_step"])
+    # llama_step only (BASELINE.json configs[4]):
+    ap.add_argument("--layers", type=int, default=32)
+    ap.add_argument("--micro-batch", type=int, default=2)
+    ap.add_argument("--seq-len", type=int, default=4096)
+    ap.add_argument("--executor", default="b200", choices=["b200", "torch"])
+    ap.add_argument("--fusion-type", default="dataflow", choices=["dataflow", "consecutive"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.workload == "llama_step":
+        thunder = import_reference()
+        if thunder is None:
+            raise SystemExit("bench.py --workload llama_step needs the reference (baseline/_ref) for thunder.jit / thunder.distributed")
+        if args.impl == "reference":
+            args.executor = "torch"
+        from baseline import train_step
+
+        if args.steps == 2000:
+            args.steps, args.warmup = 5, 3
+        train_step.run(args, thunder, ClockSampler)
+        return
     wl = WORKLOADS[args.workload]()
 
     if args.impl == "reference":
