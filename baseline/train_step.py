@@ -32,7 +32,9 @@ def region_census(thunder, jm):
     return out
 
 
-def run(args, thunder, ClockSampler):
+def run(args, thunder, ClockSampler, dist=None, emit=True):
+    """Runs the step benchmark.  With emit=True rank 0 prints the JSON line; otherwise the dict is returned (rank 0)
+    or None (other ranks), and an already initialised process group `dist` is reused and left open."""
     import warnings
 
     warnings.simplefilter("ignore")
@@ -44,11 +46,12 @@ def run(args, thunder, ClockSampler):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
-    dist = None
-    if world > 1:
+    own_pg = False
+    if world > 1 and dist is None:
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=device)
+        own_pg = True
     cfg = LlamaConfig(n_layer=args.layers)
     B, T = args.micro_batch, args.seq_len
     torch.manual_seed(1234)
@@ -133,6 +136,12 @@ def run(args, thunder, ClockSampler):
             "clocks": clocks,
         }
         line["gpu_launches"] = sum(line["b200_launches_per_step"].values()) * args.steps
-        print(json.dumps(line), flush=True)
-    if dist is not None:
+        if emit:
+            print(json.dumps(line), flush=True)
+    else:
+        line = None
+    del jm, opt, model
+    torch.cuda.empty_cache()
+    if own_pg:
         dist.destroy_process_group()
+    return line

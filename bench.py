@@ -522,6 +522,7 @@ def main():
     ap.add_argument("--executor", default="b200", choices=["b200", "torch"])
     ap.add_argument("--fusion-type", default="dataflow", choices=["dataflow", "consecutive"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train-step", action="store_true", help="skip the Llama-3-8B-shape training step that the default run appends as `train_step`")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -628,9 +629,32 @@ def main():
 
     sampler.mark_load(False)
     clocks = sampler.stop() if rank == 0 else None
+
+    # ---- second half of the metric: Llama-3-8B-shape training step in tokens/s (same process, same ranks) ----
+    train = None
+    if not args.no_train_step and args.workload == "rmsnorm":
+        wl.sets = wl.saved = None
+        torch.cuda.empty_cache()
+        try:
+            thunder = import_reference()
+            if thunder is None:
+                raise RuntimeError("reference not importable (baseline/_ref missing)")
+            from baseline import train_step
+
+            targs = argparse.Namespace(layers=args.layers, micro_batch=args.micro_batch, seq_len=args.seq_len, executor="b200",
+                                       fusion_type=args.fusion_type, steps=5, warmup=3)
+            train = train_step.run(targs, thunder, ClockSampler, dist=dist, emit=False)
+        except Exception as e:  # the region metric above must still be reported
+            train = {"error": f"{type(e).__name__}: {e}"[:500]}
     if rank == 0:
         peak, peak_src = load_peaks()
         dom = max(kernels, key=lambda k: k["us_per_launch"])
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                traffic = json.load(f).get(dom["kernel"])
+        except Exception:
+            pass
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = time_cpu(wl)
@@ -642,12 +666,14 @@ def main():
                        "sharding": "each rank runs the region on its own micro-batch; no data-path collective"},
             "roofline": {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbps"], "peak": peak, "unit": UNIT,
                          "frac": dom["achieved_gbps"] / peak, "frac_of_nominal_8TBps": dom["achieved_gbps"] / 8000.0,
-                         "traffic": None, "peak_source": peak_src},
+                         "traffic": traffic, "traffic_source": "ncu --set full capture, profiles/r1_traffic.json" if traffic else None,
+                         "algorithmic_bytes": dom["algorithmic_bytes"], "peak_source": peak_src},
             "kernels": kernels,
             "cpu_baseline": cpu,
             "e2e": e2e,
             "gpu_launches": wl.launches_per_step * args.steps,
             "clocks": clocks,
+            "train_step": train,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:

@@ -17,6 +17,36 @@ constexpr int kBaRowParts = 4;  // CTAs per SM along rows (sizes the scratch)
 constexpr float kInvSqrt2 = 0.70710678118654752440f;
 constexpr float kTwoOverSqrtPi = 1.1283791670955126f;
 
+// erf for bf16 storage: Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, far below half a bf16 ulp of a value in
+// [-1, 1]) on the hardware exp2 / reciprocal units; fp16 and fp32 storage keep erff.
+template <bool kFast>
+__device__ __forceinline__ float erf_f32(float x) {
+    if constexpr (kFast) {
+        const float ax = fabsf(x);
+        float t, e;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(ax * ax * -1.4426950408889634f));
+        float p = fmaf(1.061405429f, t, -1.453152027f);
+        p = fmaf(p, t, 1.421413741f);
+        p = fmaf(p, t, -0.284496736f);
+        p = fmaf(p, t, 0.254829592f);
+        const float r = 1.0f - p * t * e;
+        return copysignf(r, x);
+    } else {
+        return erff(x);
+    }
+}
+template <bool kFast>
+__device__ __forceinline__ float exp_negsq(float z) {
+    if constexpr (kFast) {
+        float e;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
+        return e;
+    } else {
+        return expf(-(z * z));
+    }
+}
+
 template <typename T, int kAct>
 __device__ __forceinline__ void act_fwd(float* a /* rounded pre-activation, in/out */, int n) {
     using V = Vec<T>;
@@ -29,7 +59,7 @@ __device__ __forceinline__ void act_fwd(float* a /* rounded pre-activation, in/o
         } else if constexpr (kAct == 2) {
             float z0 = a0 * kInvSqrt2, z1 = a1 * kInvSqrt2;
             V::rnd2(z0, z1);
-            float r0 = erff(z0), r1 = erff(z1);
+            float r0 = erf_f32<V::kDtype == B200K_BF16>(z0), r1 = erf_f32<V::kDtype == B200K_BF16>(z1);
             V::rnd2(r0, r1);
             r0 *= 0.5f, r1 *= 0.5f;
             V::rnd2(r0, r1);
@@ -45,6 +75,7 @@ template <typename T, int kAct>
 __device__ __forceinline__ void act_bwd(const float* a, const float* g, float* dx, int n) {
     using V = Vec<T>;
     constexpr bool kIsF32 = V::kDtype == B200K_F32;
+    constexpr bool kIsBF16 = V::kDtype == B200K_BF16;
 #pragma unroll
     for (int e = 0; e < n; e += 2) {
         const float a0 = a[e], a1 = a[e + 1], g0 = g[e], g1 = g[e + 1];
@@ -56,7 +87,7 @@ __device__ __forceinline__ void act_bwd(const float* a, const float* g, float* d
         } else {
             float z0 = a0 * kInvSqrt2, z1 = a1 * kInvSqrt2;
             V::rnd2(z0, z1);
-            float c0 = erff(z0), c1 = erff(z1);
+            float c0 = erf_f32<kIsBF16>(z0), c1 = erf_f32<kIsBF16>(z1);
             V::rnd2(c0, c1);
             c0 *= 0.5f, c1 *= 0.5f;
             V::rnd2(c0, c1);
@@ -68,7 +99,7 @@ __device__ __forceinline__ void act_bwd(const float* a, const float* g, float* d
             V::rnd2(q0, q1);
             q0 *= 0.5f, q1 *= 0.5f;
             V::rnd2(q0, q1);
-            const float pdf0 = kTwoOverSqrtPi * expf(-(z0 * z0)), pdf1 = kTwoOverSqrtPi * expf(-(z1 * z1));
+            const float pdf0 = kTwoOverSqrtPi * exp_negsq<kIsBF16>(z0), pdf1 = kTwoOverSqrtPi * exp_negsq<kIsBF16>(z1);
             float r0 = pdf0 * q0, r1 = pdf1 * q1;
             V::rnd2(r0, r1);
             r0 *= kInvSqrt2, r1 *= kInvSqrt2;

@@ -5,9 +5,9 @@
 // Hkv = G*q_per_kv when `expand` (each k/v head repeated q_per_kv times, as the reference's
 // expand+reshape materialises it) else G.  RoPE (rotate-half form) acts on the first rope_n features.
 //
-// One work item = one (b, t, input head, p) with p a vector position in the first half of the rotary
-// span: it loads vectors p and p + half (the rotation partners), so every element is read once and
-// written once; items past the rotary span copy one vector.  Consecutive threads take consecutive p,
+// A work item = (token, group, p) with p a vector position in the first half of the rotary span: for each head
+// slot of the group it loads vectors p and p + half (the rotation partners), so every element is read once and
+// written once; items past the rotary span copy one vector per slot.  Consecutive threads take consecutive p,
 // so each warp reads and writes 128-byte runs.  kW = elements per vector (8/4 for 16-byte access, 1
 // for the scalar fallback when sizes or pointers are not 16-byte friendly).
 #include "common.cuh"
@@ -50,19 +50,26 @@ __device__ __forceinline__ void rndv(float* f) {
     }
 }
 
-struct Item {
-    int64_t bt;
-    int g, slot, p;
+// Loads kept packed (one uint4 per vector) until they are consumed, so that many can be in flight per thread.
+template <int kW>
+struct Raw {
+    uint4 v;
 };
-__device__ __forceinline__ Item decode(int64_t item, int items_per_head, int slots, int G) {
-    Item it;
-    it.p = static_cast<int>(item % items_per_head);
-    int64_t r = item / items_per_head;
-    it.slot = static_cast<int>(r % slots);
-    r /= slots;
-    it.g = static_cast<int>(r % G);
-    it.bt = r / G;
-    return it;
+template <>
+struct Raw<1> {
+    float v;
+};
+template <typename T, int kW>
+__device__ __forceinline__ Raw<kW> ldraw(const T* p, int64_t elem) {
+    Raw<kW> r;
+    if constexpr (kW == 1) r.v = Vec<T>::load1(p, elem);
+    else r.v = ld_stream(p + elem);
+    return r;
+}
+template <typename T, int kW>
+__device__ __forceinline__ void unraw(const Raw<kW>& r, float* f) {
+    if constexpr (kW == 1) f[0] = r.v;
+    else Vec<T>::unpack(r.v, f);
 }
 
 // (__fmul_rn keeps the products from being contracted into FMAs, so fp32 is bit-identical to mul-then-add.)
@@ -118,8 +125,15 @@ __device__ __forceinline__ void rope_pair_bwd(const float* glo, const float* ghi
     for (int e = 0; e < kW; ++e) dhi[e] = a[e] - b[e];
 }
 
+// Work item = (token, group g, vector position p): the thread walks the group's q_per_kv + 2 head slots with the
+// cos/sin vectors of (t, p) held in registers, so the tables are fetched once per q_per_kv + 2 heads and every
+// thread has 2 * (q_per_kv + 2) independent 16-byte activations loads to overlap.
+constexpr int kTokTile = 16;  // tokens handled by neighbouring threads in the backward
+constexpr int kBwdChunk = 4;  // expanded copies gathered together in the backward
+constexpr int kMaxQpk = 6;  // slots whose loads are issued together; larger groups loop in chunks
+
 template <typename T, int kW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 rope_fwd_kernel(const T* __restrict__ qkv, const T* __restrict__ cosp, const T* __restrict__ sinp, T* __restrict__ q,
                 T* __restrict__ k, T* __restrict__ v, RopeShape s, int64_t nitems) {
     const int half = s.rope_n / 2 / kW;            // partner distance in vectors
@@ -127,51 +141,74 @@ rope_fwd_kernel(const T* __restrict__ qkv, const T* __restrict__ cosp, const T* 
     const int iph = half + tail;
     const int slots = s.qpk + 2;
     const int hkv = s.expand ? s.G * s.qpk : s.G;
+    const int nq = s.G * s.qpk;
     for (int64_t item = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; item < nitems;
          item += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const Item it = decode(item, iph, slots, s.G);
-        const int64_t b = it.bt / s.T, t = it.bt % s.T;
-        const T* src = qkv + ((it.bt * s.G + it.g) * slots + it.slot) * s.hs;
-        const bool is_q = it.slot < s.qpk, is_k = it.slot == s.qpk;
-        const bool paired = it.p < half;
-        const int e0 = paired ? it.p * kW : (s.rope_n + (it.p - half) * kW);
+        const int p = static_cast<int>(item % iph);
+        const int64_t r = item / iph;
+        const int g = static_cast<int>(r % s.G);
+        const int64_t bt = r / s.G;
+        const int64_t b = bt / s.T, t = bt % s.T;
+        const bool paired = p < half;
+        const int e0 = paired ? p * kW : (s.rope_n + (p - half) * kW);
         const int e1 = e0 + half * kW;
-        float lo[kW], hi[kW] = {}, olo[kW], ohi[kW];
-        ldv<T, kW>(src, e0, lo, true);
-        if (paired) ldv<T, kW>(src, e1, hi, true);
-        if (paired && (is_q || is_k)) {
-            float clo[kW], chi[kW], slo[kW], shi[kW];
+        const T* grp = qkv + (bt * s.G + g) * (static_cast<int64_t>(slots) * s.hs);
+        float clo[kW], chi[kW], slo[kW], shi[kW];
+        if (paired) {
             ldv<T, kW>(cosp, t * s.rope_n + e0, clo, false);
             ldv<T, kW>(cosp, t * s.rope_n + e1, chi, false);
             ldv<T, kW>(sinp, t * s.rope_n + e0, slo, false);
             ldv<T, kW>(sinp, t * s.rope_n + e1, shi, false);
-            rope_pair<T, kW>(lo, hi, clo, chi, slo, shi, olo, ohi);
-        } else {
-#pragma unroll
-            for (int e = 0; e < kW; ++e) {
-                olo[e] = lo[e];
-                ohi[e] = hi[e];
-            }
         }
-        if (is_q) {
-            T* dst = q + ((b * (s.G * s.qpk) + it.g * s.qpk + it.slot) * s.T + t) * s.hs;
-            stv<T, kW>(dst, e0, olo);
-            if (paired) stv<T, kW>(dst, e1, ohi);
-        } else {
-            T* base = is_k ? k : v;
-            const int reps = s.expand ? s.qpk : 1;
-            for (int r = 0; r < reps; ++r) {
-                const int head = s.expand ? it.g * s.qpk + r : it.g;
-                T* dst = base + ((b * hkv + head) * s.T + t) * s.hs;
-                stv<T, kW>(dst, e0, olo);
-                if (paired) stv<T, kW>(dst, e1, ohi);
+        for (int s0 = 0; s0 < slots; s0 += kMaxQpk) {
+            Raw<kW> rlo[kMaxQpk], rhi[kMaxQpk];
+#pragma unroll
+            for (int j = 0; j < kMaxQpk; ++j) {
+                if (s0 + j < slots) {
+                    const T* src = grp + static_cast<int64_t>(s0 + j) * s.hs;
+                    rlo[j] = ldraw<T, kW>(src, e0);
+                    rhi[j] = ldraw<T, kW>(src, paired ? e1 : e0);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kMaxQpk; ++j) {
+                const int slot = s0 + j;
+                if (slot < slots) {
+                    const bool is_q = slot < s.qpk, is_k = slot == s.qpk;
+                    float lo[kW], hi[kW], olo[kW], ohi[kW];
+                    unraw<T, kW>(rlo[j], lo);
+                    unraw<T, kW>(rhi[j], hi);
+                    if (paired && (is_q || is_k)) {
+                        rope_pair<T, kW>(lo, hi, clo, chi, slo, shi, olo, ohi);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < kW; ++e) olo[e] = lo[e], ohi[e] = hi[e];
+                    }
+                    if (is_q) {
+                        T* dst = q + ((b * nq + g * s.qpk + slot) * s.T + t) * s.hs;
+                        stv<T, kW>(dst, e0, olo);
+                        if (paired) stv<T, kW>(dst, e1, ohi);
+                    } else {
+                        T* base = is_k ? k : v;
+                        const int reps = s.expand ? s.qpk : 1;
+                        for (int rr = 0; rr < reps; ++rr) {
+                            const int head = s.expand ? g * s.qpk + rr : g;
+                            T* dst = base + ((b * hkv + head) * s.T + t) * s.hs;
+                            stv<T, kW>(dst, e0, olo);
+                            if (paired) stv<T, kW>(dst, e1, ohi);
+                        }
+                    }
+                }
             }
         }
     }
 }
 
+// Backward work item = (token, group, pass, p): pass 0 turns the group's q cotangents into dq (one output per
+// head), pass 1 / 2 fold the q_per_kv expanded copies of dk / dv into the single k / v slot (fp32 sum, rounded
+// once, as the expand's vjp does).  Passes are separate threads so their gathers overlap.
 template <typename T, int kW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128, 4)
 rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __restrict__ dv, const T* __restrict__ cosp,
                 const T* __restrict__ sinp, T* __restrict__ dqkv, RopeShape s, int64_t nitems) {
     const int half = s.rope_n / 2 / kW;
@@ -179,16 +216,30 @@ rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __r
     const int iph = half + tail;
     const int slots = s.qpk + 2;
     const int hkv = s.expand ? s.G * s.qpk : s.G;
+    const int nq = s.G * s.qpk;
     for (int64_t item = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; item < nitems;
          item += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const Item it = decode(item, iph, slots, s.G);
-        const int64_t b = it.bt / s.T, t = it.bt % s.T;
-        T* dst = dqkv + ((it.bt * s.G + it.g) * slots + it.slot) * s.hs;
-        const bool is_q = it.slot < s.qpk, is_k = it.slot == s.qpk;
-        const bool paired = it.p < half;
-        const bool roped = paired && (is_q || is_k);
-        const int e0 = paired ? it.p * kW : (s.rope_n + (it.p - half) * kW);
+        // p fastest, then kTokTile consecutive tokens: the cotangents are [B, heads, T, hs], so neighbouring threads
+        // read neighbouring tokens of one head — contiguous kTokTile * hs runs instead of isolated head rows
+        const int p = static_cast<int>(item % iph);
+        int64_t r = item / iph;
+        const int tt = static_cast<int>(r % kTokTile);
+        r /= kTokTile;
+        const int pass = static_cast<int>(r % 3);
+        r /= 3;
+        const int g = static_cast<int>(r % s.G);
+        const int64_t bt = (r / s.G) * kTokTile + tt;
+        if (bt >= s.B * s.T) continue;
+        const int64_t b = bt / s.T, t = bt % s.T;
+        const bool paired = p < half;
+        const int e0 = paired ? p * kW : (s.rope_n + (p - half) * kW);
         const int e1 = e0 + half * kW;
+        T* grp = dqkv + (bt * s.G + g) * (static_cast<int64_t>(slots) * s.hs);
+        const T* base = pass == 0 ? dq : (pass == 1 ? dk : dv);
+        const int heads_total = pass == 0 ? nq : hkv;
+        const int nsrc = pass == 0 ? s.qpk : (s.expand ? s.qpk : 1);
+        const int head0 = pass == 0 ? g * s.qpk : (s.expand ? g * s.qpk : g);
+        const bool roped = paired && pass < 2;
         float clo[kW], chi[kW], slo[kW], shi[kW];
         if (roped) {
             ldv<T, kW>(cosp, t * s.rope_n + e0, clo, false);
@@ -196,44 +247,51 @@ rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __r
             ldv<T, kW>(sinp, t * s.rope_n + e0, slo, false);
             ldv<T, kW>(sinp, t * s.rope_n + e1, shi, false);
         }
-        float olo[kW], ohi[kW];
-        if (is_q) {
-            const T* src = dq + ((b * (s.G * s.qpk) + it.g * s.qpk + it.slot) * s.T + t) * s.hs;
-            float glo[kW], ghi[kW] = {};
-            ldv<T, kW>(src, e0, glo, true);
-            if (paired) ldv<T, kW>(src, e1, ghi, true);
-            if (roped) {
-                rope_pair_bwd<T, kW>(glo, ghi, clo, chi, slo, shi, olo, ohi);
-            } else {
+        float acc_lo[kW], acc_hi[kW];
 #pragma unroll
-                for (int e = 0; e < kW; ++e) olo[e] = glo[e], ohi[e] = ghi[e];
-            }
-        } else {
-            // k / v: the expand's vjp sums the q_per_kv copies in fp32 and rounds once
-            const T* base = is_k ? dk : dv;
-            const int reps = s.expand ? s.qpk : 1;
+        for (int e = 0; e < kW; ++e) acc_lo[e] = 0.f, acc_hi[e] = 0.f;
+        for (int s0 = 0; s0 < nsrc; s0 += kBwdChunk) {
+            Raw<kW> rlo[kBwdChunk], rhi[kBwdChunk];
 #pragma unroll
-            for (int e = 0; e < kW; ++e) olo[e] = 0.f, ohi[e] = 0.f;
-            for (int r = 0; r < reps; ++r) {
-                const int head = s.expand ? it.g * s.qpk + r : it.g;
-                const T* src = base + ((b * hkv + head) * s.T + t) * s.hs;
-                float glo[kW], ghi[kW] = {}, dlo[kW], dhi[kW];
-                ldv<T, kW>(src, e0, glo, true);
-                if (paired) ldv<T, kW>(src, e1, ghi, true);
-                if (roped) {
-                    rope_pair_bwd<T, kW>(glo, ghi, clo, chi, slo, shi, dlo, dhi);
-                    rndv<T, kW>(dlo);
-                    rndv<T, kW>(dhi);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < kW; ++e) dlo[e] = glo[e], dhi[e] = ghi[e];
+            for (int j = 0; j < kBwdChunk; ++j) {
+                if (s0 + j < nsrc) {
+                    const T* src = base + ((b * heads_total + head0 + s0 + j) * s.T + t) * s.hs;
+                    rlo[j] = ldraw<T, kW>(src, e0);
+                    rhi[j] = ldraw<T, kW>(src, paired ? e1 : e0);
                 }
+            }
 #pragma unroll
-                for (int e = 0; e < kW; ++e) olo[e] += dlo[e], ohi[e] += dhi[e];
+            for (int j = 0; j < kBwdChunk; ++j) {
+                if (s0 + j < nsrc) {
+                    float glo[kW], ghi[kW], dlo[kW], dhi[kW];
+                    unraw<T, kW>(rlo[j], glo);
+                    unraw<T, kW>(rhi[j], ghi);
+                    if (roped) {
+                        rope_pair_bwd<T, kW>(glo, ghi, clo, chi, slo, shi, dlo, dhi);
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < kW; ++e) dlo[e] = glo[e], dhi[e] = ghi[e];
+                    }
+                    if (pass == 0) {
+                        T* dst = grp + static_cast<int64_t>(s0 + j) * s.hs;
+                        stv<T, kW>(dst, e0, dlo);
+                        if (paired) stv<T, kW>(dst, e1, dhi);
+                    } else {
+                        if (roped) {
+                            rndv<T, kW>(dlo);
+                            rndv<T, kW>(dhi);
+                        }
+#pragma unroll
+                        for (int e = 0; e < kW; ++e) acc_lo[e] += dlo[e], acc_hi[e] += dhi[e];
+                    }
+                }
             }
         }
-        stv<T, kW>(dst, e0, olo);
-        if (paired) stv<T, kW>(dst, e1, ohi);
+        if (pass > 0) {
+            T* dst = grp + static_cast<int64_t>(s.qpk + pass - 1) * s.hs;
+            stv<T, kW>(dst, e0, acc_lo);
+            if (paired) stv<T, kW>(dst, e1, acc_hi);
+        }
     }
 }
 
@@ -249,24 +307,25 @@ int run(bool fwd, const void* a0, const void* a1, const void* a2, const void* co
                      aligned16(cosp) && aligned16(sinp) && aligned16(o0) && aligned16(o1) && aligned16(o2);
     const int w = vec ? kE : 1;
     const int64_t iph = s.rope_n / 2 / w + (s.hs - s.rope_n) / w;
-    const int64_t nitems = s.B * s.T * s.G * (s.qpk + 2) * iph;
+    // forward: (token, group, vector position); backward: (token tile, group, pass, token in tile, vector position)
+    const int64_t nitems = fwd ? s.B * s.T * s.G * iph : ((s.B * s.T + kTokTile - 1) / kTokTile) * kTokTile * s.G * iph * 3;
     if (nitems == 0) return 0;
-    const int64_t want = (nitems + 255) / 256;
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 32;
+    const int64_t want = (nitems + 127) / 128;
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 64;
     const int grid = static_cast<int>(want < cap ? want : cap);
     if (fwd) {
         if (vec)
-            rope_fwd_kernel<T, kE><<<grid, 256, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(cosp), static_cast<const T*>(sinp),
+            rope_fwd_kernel<T, kE><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(cosp), static_cast<const T*>(sinp),
                                                          static_cast<T*>(o0), static_cast<T*>(o1), static_cast<T*>(o2), s, nitems);
         else
-            rope_fwd_kernel<T, 1><<<grid, 256, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(cosp), static_cast<const T*>(sinp),
+            rope_fwd_kernel<T, 1><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(cosp), static_cast<const T*>(sinp),
                                                         static_cast<T*>(o0), static_cast<T*>(o1), static_cast<T*>(o2), s, nitems);
     } else {
         if (vec)
-            rope_bwd_kernel<T, kE><<<grid, 256, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
+            rope_bwd_kernel<T, kE><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
                                                          static_cast<const T*>(cosp), static_cast<const T*>(sinp), static_cast<T*>(o0), s, nitems);
         else
-            rope_bwd_kernel<T, 1><<<grid, 256, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
+            rope_bwd_kernel<T, 1><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
                                                         static_cast<const T*>(cosp), static_cast<const T*>(sinp), static_cast<T*>(o0), s, nitems);
     }
     return launch_status();

@@ -12,19 +12,47 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kUnroll = 4;
 
-// silu(a) = a / (1 + exp(-a)) in fp32, exactly the expression ATen evaluates.
-__device__ __forceinline__ float silu_f32(float a) { return a / (1.0f + expf(-a)); }
+// silu(a) = a / (1 + exp(-a)) in fp32, the expression ATen evaluates.  For bf16 storage every result is rounded
+// to 8 significant bits right away, so the 2-ulp hardware exp2 / reciprocal forms are used (a flip of that
+// rounding needs the fp32 value within 2^-22 of a rounding boundary, and costs one bf16 ulp, well inside the
+// bf16 tolerance); fp16 and fp32 storage keep expf and IEEE division.
+template <bool kFast>
+__device__ __forceinline__ float exp_neg(float a) {
+    if constexpr (kFast) {
+        float y;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(a * -1.4426950408889634f));
+        return y;
+    } else {
+        return expf(-a);
+    }
+}
+template <bool kFast>
+__device__ __forceinline__ float recip(float x) {
+    if constexpr (kFast) {
+        float y;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+        return y;
+    } else {
+        return 1.0f / x;
+    }
+}
+template <bool kFast>
+__device__ __forceinline__ float silu_f32(float a) {
+    if constexpr (kFast) return a * recip<true>(1.0f + exp_neg<true>(a));
+    else return a / (1.0f + expf(-a));
+}
 
 template <typename T>
 __device__ __forceinline__ void swiglu_fwd_vec(const uint4& av, const uint4& bv, uint4& ov) {
     using V = Vec<T>;
     constexpr int kE = V::kElems;
+    constexpr bool kFast = V::kDtype == B200K_BF16;
     float a[kE], b[kE], o[kE];
     V::unpack(av, a);
     V::unpack(bv, b);
 #pragma unroll
     for (int e = 0; e < kE; e += 2) {
-        float u0 = silu_f32(a[e]), u1 = silu_f32(a[e + 1]);
+        float u0 = silu_f32<kFast>(a[e]), u1 = silu_f32<kFast>(a[e + 1]);
         V::rnd2(u0, u1);  // silu result is a tensor of the storage dtype
         o[e] = u0 * b[e];
         o[e + 1] = u1 * b[e + 1];
@@ -36,24 +64,25 @@ template <typename T>
 __device__ __forceinline__ void swiglu_bwd_vec(const uint4& av, const uint4& bv, const uint4& gv, uint4& dav, uint4& dbv) {
     using V = Vec<T>;
     constexpr int kE = V::kElems;
+    constexpr bool kFast = V::kDtype == B200K_BF16;
     float a[kE], b[kE], g[kE], da[kE], db[kE];
     V::unpack(av, a);
     V::unpack(bv, b);
     V::unpack(gv, g);
 #pragma unroll
     for (int e = 0; e < kE; e += 2) {
-        float u0 = silu_f32(a[e]), u1 = silu_f32(a[e + 1]);
+        float u0 = silu_f32<kFast>(a[e]), u1 = silu_f32<kFast>(a[e + 1]);
         V::rnd2(u0, u1);
         db[e] = u0 * g[e];
         db[e + 1] = u1 * g[e + 1];
         float gu0 = b[e] * g[e], gu1 = b[e + 1] * g[e + 1];
         V::rnd2(gu0, gu1);
         // silu vjp evaluated op by op in the storage dtype (clang.silu = a * sigmoid(a)):
-        float t0 = expf(-a[e]), t1 = expf(-a[e + 1]);
+        float t0 = exp_neg<kFast>(a[e]), t1 = exp_neg<kFast>(a[e + 1]);
         V::rnd2(t0, t1);  // exp(-a)
         t0 = 1.0f + t0, t1 = 1.0f + t1;
         V::rnd2(t0, t1);  // 1 + exp(-a)
-        float s0 = 1.0f / t0, s1 = 1.0f / t1;
+        float s0 = recip<kFast>(t0), s1 = recip<kFast>(t1);
         V::rnd2(s0, s1);  // sigmoid
         float p0 = gu0 * s0, p1 = gu1 * s1;
         V::rnd2(p0, p1);  // g * sigmoid
@@ -100,7 +129,7 @@ template <typename T>
 __global__ void __launch_bounds__(kThreads)
 swiglu_bwd_kernel(const T* __restrict__ a, const T* __restrict__ b, const T* __restrict__ g, T* __restrict__ da,
                   T* __restrict__ db, int64_t nvec) {
-    constexpr int kU = 2;
+    constexpr int kU = 4;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kThreads * kU;
     for (int64_t base = static_cast<int64_t>(blockIdx.x) * kThreads * kU + threadIdx.x; base < nvec; base += stride) {
         uint4 av[kU], bv[kU], gv[kU];
@@ -132,7 +161,7 @@ __global__ void swiglu_fwd_tail_kernel(const T* a, const T* b, T* out, int64_t b
     using V = Vec<T>;
     for (int64_t i = begin + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-        const float u = V::rnd(silu_f32(V::load1(a, i)));
+        const float u = V::rnd(silu_f32<false>(V::load1(a, i)));
         V::store1(out, i, u * V::load1(b, i));
     }
 }
@@ -143,7 +172,7 @@ __global__ void swiglu_bwd_tail_kernel(const T* a, const T* b, const T* g, T* da
     for (int64_t i = begin + blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
          i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
         const float x = V::load1(a, i), y = V::load1(b, i), gg = V::load1(g, i);
-        const float u = V::rnd(silu_f32(x));
+        const float u = V::rnd(silu_f32<false>(x));
         V::store1(db, i, u * gg);
         const float gu = V::rnd(y * gg);
         const float t = V::rnd(1.0f + V::rnd(expf(-x)));
@@ -185,7 +214,7 @@ int run_bwd(const void* a, const void* b, const void* g, void* da, void* db, int
     const bool vec_ok = aligned16(a) && aligned16(b) && aligned16(g) && aligned16(da) && aligned16(db);
     const int64_t nvec = vec_ok ? n / kE : 0;
     if (nvec > 0) {
-        swiglu_bwd_kernel<T><<<grid_for(nvec, kThreads * 2), kThreads, 0, st>>>(
+        swiglu_bwd_kernel<T><<<grid_for(nvec, kThreads * 4), kThreads, 0, st>>>(
             static_cast<const T*>(a), static_cast<const T*>(b), static_cast<const T*>(g), static_cast<T*>(da), static_cast<T*>(db), nvec);
         if (int rc = launch_status()) return rc;
     }

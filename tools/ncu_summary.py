@@ -1,0 +1,17 @@
+"""Summarise an ncu report: per-kernel duration, DRAM bytes and throughput (raw page) — used to fill profiles/."""
+import csv, subprocess, sys, collections
+
+rep = sys.argv[1]
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(raw.splitlines()))
+hdr, units, data = rows[0], rows[1], rows[2:]
+col = {h: i for i, h in enumerate(hdr)}
+want = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+        "launch__grid_size", "launch__block_size", "smsp__issue_active.avg.pct_of_peak_sustained_active"]
+for d in data:
+    name = d[col["Kernel Name"]]
+    print("kernel:", name[:110])
+    for w in want:
+        if w in col:
+            print(f"  {w:70s} {d[col[w]]:>14s} {units[col[w]]}")
