@@ -19,6 +19,7 @@ import ctypes
 import hashlib
 import itertools
 import struct
+import threading
 from dataclasses import dataclass, field
 
 import torch
@@ -321,24 +322,76 @@ def _collapse(shape, strides_list):
     return out_shape, out_strides
 
 
+class _Plan:
+    """Everything about one launch that depends only on the operands' (shape, stride, dtype): the collapsed
+    iteration box, per-operand strides, which operands need a contiguous copy first, and a prefilled program
+    struct whose pointers are patched per call."""
+
+    __slots__ = ("P", "contig_fix", "lock")
+
+    def __init__(self, P, contig_fix):
+        self.P, self.contig_fix, self.lock = P, contig_fix, threading.Lock()
+
+
 class PwLaunch:
-    """A compiled program bound to its region: ``run(env)`` reads input tensors from ``env`` by name and
-    returns {output name: new contiguous tensor}."""
+    """A compiled program bound to its region: ``run(env)`` reads input tensors from ``env`` by name and returns
+    {output name: new contiguous tensor}.  Launch plans are cached per operand descriptor — the analogue of the
+    reference's ``lru_cache`` keyed on ``to_runtime_descriptors`` (nvfuserex_impl.py:505-521, 622-625), needed
+    because trace proxies carry no strides."""
+
+    MAX_PLANS = 2048
 
     def __init__(self, spec: PwProgramSpec):
         self.spec = spec
+        self._plans: dict = {}
+        self.plan_hits = 0
+        self.plan_misses = 0
 
-    def _leaf_strides(self, t: torch.Tensor, mapping, ndim):
+    @staticmethod
+    def _leaf_strides(t: torch.Tensor, mapping, ndim):
         st = [0] * ndim
         for i, d in enumerate(mapping):
             if t.shape[i] != 1:
                 st[d] = t.stride(i)
         return st
 
-    def run(self, env: dict) -> dict:
+    def _build_plan(self, tensors) -> _Plan:
         spec = self.spec
         shape = list(spec.iter_shape)
         nd = len(shape)
+        contig = [0] * nd
+        acc = 1
+        for d in range(nd - 1, -1, -1):
+            contig[d] = acc
+            acc *= shape[d]
+        in_strides = [self._leaf_strides(t, m, nd) for t, (_, m) in zip(tensors, spec.leaves)]
+        cshape, cstrides = _collapse(shape, in_strides + [contig])
+        contig_fix = False
+        if len(cshape) > 3:
+            # more than three independent strides: every operand gets the contiguous broadcast layout first
+            # (a strided copy by torch; rare — needs e.g. several differently permuted inputs)
+            contig_fix = True
+            cshape, cstrides = _collapse(shape, [list(contig) for _ in tensors] + [contig])
+        while len(cshape) < 3:
+            cshape.insert(0, 1)
+            for st in cstrides:
+                st.insert(0, 0)
+        P = _Program()
+        P.d0, P.d1, P.d2 = cshape
+        P.n_in, P.n_out, P.n_code, P.n_reg = len(tensors), len(spec.outputs), len(spec.code), spec.n_reg
+        for k, (t, st) in enumerate(zip(tensors, cstrides[:-1])):
+            P.inp[k] = _Operand(0, st[0], st[1], st[2], DTYPE_CODE[t.dtype])
+        so = [cshape[1] * cshape[2], cshape[2], 1]  # outputs are freshly allocated, contiguous over the collapsed box
+        for k, (name, dt, reg) in enumerate(spec.outputs):
+            P.out[k] = _Operand(0, so[0], so[1], so[2], DTYPE_CODE[dt])
+            P.out_reg[k] = reg
+        for k, w in enumerate(spec.code):
+            P.code[k] = w
+        return _Plan(P, contig_fix)
+
+    def run(self, env: dict) -> dict:
+        spec = self.spec
+        shape = spec.iter_shape
         tensors = []
         for name, mapping in spec.leaves:
             t = env[name]
@@ -349,21 +402,20 @@ class PwLaunch:
             tensors.append(t)
         dev = tensors[0].device if tensors else torch.device("cuda", torch.cuda.current_device())
         outs = {name: torch.empty(shape, dtype=dt, device=dev) for name, dt, _ in spec.outputs}
-        numel = 1
-        for n in shape:
-            numel *= n
-        if numel == 0:
+        if 0 in shape:
             return outs
-        in_strides = [self._leaf_strides(t, m, nd) for t, (_, m) in zip(tensors, spec.leaves)]
-        contig = [0] * nd
-        acc = 1
-        for d in range(nd - 1, -1, -1):
-            contig[d] = acc
-            acc *= shape[d]
-        cshape, cstrides = _collapse(shape, in_strides + [contig])
-        if len(cshape) > 3:
-            # more than three independent strides: give every operand the contiguous broadcast layout first
-            # (a strided copy by torch; rare — needs e.g. several differently permuted inputs)
+        # pointers enter the key only through their alignment class (vector path needs 16 B / 8 B alignment)
+        key = tuple((t.shape, t.stride(), t.dtype, t.data_ptr() % 16 == 0) for t in tensors)
+        plan = self._plans.get(key)
+        if plan is None:
+            self.plan_misses += 1
+            plan = self._build_plan(tensors)
+            if len(self._plans) < self.MAX_PLANS:
+                self._plans[key] = plan
+        else:
+            self.plan_hits += 1
+        if plan.contig_fix:
+            nd = len(shape)
             fixed = []
             for t, (_, m) in zip(tensors, spec.leaves):
                 full = [1] * nd
@@ -371,23 +423,13 @@ class PwLaunch:
                     full[d] = t.shape[i]
                 fixed.append(t.reshape(full).expand(shape).contiguous())
             tensors = fixed
-            cshape, cstrides = _collapse(shape, [list(contig) for _ in tensors] + [contig])
-        while len(cshape) < 3:
-            cshape.insert(0, 1)
-            for s in cstrides:
-                s.insert(0, 0)
-        P = _Program()
-        P.d0, P.d1, P.d2 = cshape
-        P.n_in, P.n_out, P.n_code, P.n_reg = len(tensors), len(spec.outputs), len(spec.code), spec.n_reg
-        for k, (t, s) in enumerate(zip(tensors, cstrides[:-1])):
-            P.inp[k] = _Operand(t.data_ptr(), s[0], s[1], s[2], DTYPE_CODE[t.dtype])
-        so = [cshape[1] * cshape[2], cshape[2], 1]  # outputs are freshly allocated, contiguous over the collapsed box
-        for k, (name, dt, reg) in enumerate(spec.outputs):
-            P.out[k] = _Operand(outs[name].data_ptr(), so[0], so[1], so[2], DTYPE_CODE[dt])
-            P.out_reg[k] = reg
-        for k, w in enumerate(spec.code):
-            P.code[k] = w
-        with torch.cuda.device(dev):
-            rc = _lib.lib().b200k_pointwise(ctypes.byref(P), torch.cuda.current_stream(dev).cuda_stream)
+        with plan.lock:  # the struct is shared between calls; the launch copies it before returning
+            P = plan.P
+            for k, t in enumerate(tensors):
+                P.inp[k].ptr = t.data_ptr()
+            for k, (name, _, _) in enumerate(spec.outputs):
+                P.out[k].ptr = outs[name].data_ptr()
+            with torch.cuda.device(dev):
+                rc = _lib.lib().b200k_pointwise(ctypes.byref(P), torch.cuda.current_stream(dev).cuda_stream)
         _lib.check(rc, "b200k_pointwise")
         return outs

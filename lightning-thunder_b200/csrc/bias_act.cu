@@ -11,7 +11,7 @@
 namespace b200k {
 namespace {
 
-constexpr int kBaThreads = 256;
+constexpr int kBaThreads = 512;
 constexpr int kBaVpl = 2;
 constexpr int kBaRowParts = 4;  // CTAs per SM along rows (sizes the scratch)
 constexpr float kInvSqrt2 = 0.70710678118654752440f;
@@ -117,12 +117,12 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
                 float* __restrict__ partial, int64_t rows, int nvec) {
     using V = Vec<T>;
     constexpr int kE = V::kElems;
-    const int tid = threadIdx.x;
-    const int v0 = blockIdx.y * (kBaThreads * kBaVpl) + tid;
+    const int tid = threadIdx.x, nthr = blockDim.x;
+    const int v0 = blockIdx.y * (nthr * kBaVpl) + tid;
     float bf[kBaVpl][kE], acc[kBaVpl][kE];
 #pragma unroll
     for (int i = 0; i < kBaVpl; ++i) {
-        const int v = v0 + i * kBaThreads;
+        const int v = v0 + i * nthr;
 #pragma unroll
         for (int e = 0; e < kE; ++e) bf[i][e] = 0.f, acc[i][e] = 0.f;
         if (kHasBias && v < nvec) V::unpack(ld_keep(reinterpret_cast<const uint4*>(bias) + v), bf[i]);
@@ -131,7 +131,7 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
         uint4 xv[kBaVpl], gv[kBaVpl];
 #pragma unroll
         for (int i = 0; i < kBaVpl; ++i) {
-            const int v = v0 + i * kBaThreads;
+            const int v = v0 + i * nthr;
             if (v < nvec) {
                 xv[i] = ld_stream(reinterpret_cast<const uint4*>(x) + row * nvec + v);
                 if constexpr (kBwd) gv[i] = ld_stream(reinterpret_cast<const uint4*>(g) + row * nvec + v);
@@ -139,7 +139,7 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
         }
 #pragma unroll
         for (int i = 0; i < kBaVpl; ++i) {
-            const int v = v0 + i * kBaThreads;
+            const int v = v0 + i * nthr;
             if (v < nvec) {
                 float a[kE], o[kE];
                 V::unpack(xv[i], a);
@@ -177,7 +177,7 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
         float* prow = partial + static_cast<int64_t>(blockIdx.x) * nvec * kE;
 #pragma unroll
         for (int i = 0; i < kBaVpl; ++i) {
-            const int v = v0 + i * kBaThreads;
+            const int v = v0 + i * nthr;
             if (v < nvec) {
 #pragma unroll
                 for (int q = 0; q < kE / 4; ++q)
@@ -238,14 +238,17 @@ int run(const void* x, const void* bias, const void* g, void* out, void* dbias, 
         return launch_status();
     }
     const int nvec = static_cast<int>(hidden / V::kElems);
+    // balanced column tiles: as few tiles as fit kBaThreads * kBaVpl vectors, each with just enough threads
     const int col_tiles = (nvec + kBaThreads * kBaVpl - 1) / (kBaThreads * kBaVpl);
+    const int per_tile = (nvec + col_tiles - 1) / col_tiles;
+    const int threads = ((per_tile + kBaVpl - 1) / kBaVpl + 31) / 32 * 32;
     const int parts = row_parts(rows, col_tiles);
     const bool need_partial = kBwd && bias != nullptr;
     if (need_partial && (scratch == nullptr || !aligned16(scratch) || scratch_bytes < static_cast<int64_t>(parts) * hidden * 4))
         return B200K_ESCRATCH;
     const dim3 grid(parts, col_tiles);
     auto go = [&](auto kernel) {
-        kernel<<<grid, kBaThreads, 0, st>>>(static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(g),
+        kernel<<<grid, threads, 0, st>>>(static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(g),
                                            static_cast<T*>(out), static_cast<float*>(scratch), rows, nvec);
         return launch_status();
     };

@@ -125,3 +125,17 @@ def test_long_program_is_split_not_rejected():
 def test_empty_tensor():
     out = _run({"x": torch.empty(0, 8)}, [PwNode("neg", "o", F32, (0, 8), ("x",))], ["o"])["o"]
     assert out.shape == (0, 8)
+
+
+def test_launch_plans_are_cached_per_descriptor():
+    shape = (16, 64)
+    x = torch.randn(*shape, device=DEV)
+    (spec,) = compile_chain({"x": (F32, shape)}, [PwNode("exp", "o", F32, shape, ("x",))], ["o"])
+    launch = PwLaunch(spec)
+    launch.run({"x": x})
+    launch.run({"x": torch.randn(*shape, device=DEV)})  # same shape/stride/dtype: plan reused
+    assert (launch.plan_misses, launch.plan_hits) == (1, 1)
+    xt = torch.randn(64, 16, device=DEV).t()  # same shape, other strides: new plan, still correct
+    out = launch.run({"x": xt})["o"]
+    assert (launch.plan_misses, launch.plan_hits) == (2, 1)
+    torch.testing.assert_close(out, torch.exp(xt))
