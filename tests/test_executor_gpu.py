@@ -163,3 +163,42 @@ def test_tiny_llama_forward_backward(fusion_type):
         # in the aggregate, relative to the gradient's scale
         err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
         assert err.item() < 2e-2, f"grad {n}: relative error {err.item():.3e}"
+
+
+def test_llama3_8b_block_full_size():
+    """BASELINE.json configs[2]: one LitGPT-style Llama-3-8B transformer block (n_embd 4096, 32 heads / 8 KV groups x 128,
+    intermediate 14336), bf16, batch 2 x seq 4096, forward + backward, b200 regions against the torch executor."""
+    from baseline.llama_model import LLAMA3_8B, Block, build_rope_cache
+    from thunder.executors.sdpaex import sdpa_ex
+
+    cfg = LLAMA3_8B
+    torch.manual_seed(0)
+    block = Block(cfg).to(DEV).to(BF)
+    B, T = 2, 4096
+    cos, sin = build_rope_cache(T, cfg.rope_n_elem, base=cfg.rope_base, device=DEV, dtype=BF)
+    x0 = (torch.randn(B, T, cfg.n_embd, device=DEV) * 0.5).to(BF)
+    cot = torch.randn(B, T, cfg.n_embd, device=DEV).to(BF)
+    res = {}
+    for name, execs in (("b200", [sdpa_ex, b200.ex]), ("torch", [sdpa_ex, "torch"])):
+        block.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        jb = thunder.jit(block, executors=execs, fusion_type="dataflow")
+        y = jb(x, cos, sin)
+        y.backward(cot)
+        res[name] = (y.detach(), x.grad.detach(), {n: p.grad.detach().clone() for n, p in block.named_parameters()}, jb)
+    torch.cuda.synchronize()
+    jb = res["b200"][3]
+    fk = [k for _, ks in fusions(thunder.last_traces(jb)[-1]) for k in ks]
+    bk = [k for _, ks in fusions(thunder.last_backward_traces(jb)[-1]) for k in ks]
+    # region census of SURVEY Appendix C, all on hand-written kernels
+    assert sorted(fk) == sorted(["b200_rms_norm_fwd", "b200_qkv_split_rope", "b200_rms_norm_fwd+residual", "b200k_swiglu_fwd", "b200k_pointwise"])
+    assert "b200k_swiglu_bwd" in bk and "b200_qkv_rope_bwd" in bk and bk.count("b200_rms_norm_bwd") + bk.count("b200_rms_norm_bwd+residual") == 2
+
+    def rel(a, b):
+        return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
+
+    # outputs of GEMM/attention chains over bf16 activations that differ by an ulp here and there: aggregate error
+    assert rel(res["b200"][0], res["torch"][0]) < 1e-2
+    assert rel(res["b200"][1], res["torch"][1]) < 2e-2
+    for n, g in res["b200"][2].items():
+        assert rel(g, res["torch"][2][n]) < 2e-2, f"grad {n}"
