@@ -183,21 +183,32 @@ B200K_API int b200k_qkv_rope_bwd(const void* dq, const void* dk, const void* dv,
  * bias + activation forward — SURVEY §8 row a11.  act: 0 = none, 1 = relu (ltorch.relu ->
  * where(a > 0, a, 0)), 2 = gelu, erf form (thunder/torch/__init__.py:2071-2082).
  *   a = round_T(x + bias)  (a = x when bias == NULL);  out = act(a) with one round_T per ltorch op.
- * x, out [rows, hidden]; bias [hidden].
+ * x, out [rows, hidden]; bias [hidden]; pre_out (may be NULL): also receives a, the pre-activation that
+ * autodiff saves for the backward.
  * --------------------------------------------------------------------------------------------- */
-B200K_API int b200k_bias_act_fwd(const void* x, const void* bias, void* out, int64_t rows, int64_t hidden, int act,
-                                 int dtype, void* stream);
+B200K_API int b200k_bias_act_fwd(const void* x, const void* bias, void* out, void* pre_out, int64_t rows, int64_t hidden,
+                                 int act, int dtype, void* stream);
 
 /* Scratch bytes b200k_bias_act_bwd needs when bias != NULL. */
 B200K_API int64_t b200k_bias_act_bwd_scratch_bytes(int64_t rows, int64_t hidden);
 
 /* ---------------------------------------------------------------------------------------------
- * bias + activation backward — SURVEY §8 row a11.  dx = act'(a) applied to g with the reference's
- * rounding points; dbias = round_T(sum_rows f32(dx)) (not written when bias == NULL).
+ * bias + activation backward — SURVEY §8 row a11.  With a = round_T(x + bias) (a = x when bias == NULL, i.e.
+ * when the caller passes the saved pre-activation): dx = act'(a) applied to g with the reference's rounding
+ * points; dbias = round_T(sum_rows f32(dx)), written iff dbias != NULL (then scratch is required).
  * scratch as for b200k_rmsnorm_bwd (contents ignored on entry, unspecified on exit).
  * --------------------------------------------------------------------------------------------- */
 B200K_API int b200k_bias_act_bwd(const void* x, const void* bias, const void* g, void* dx, void* dbias, void* scratch,
                                  int64_t scratch_bytes, int64_t rows, int64_t hidden, int act, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Column sum — the `sum` over the leading dims that follows a pointwise region (bias gradients and the like;
+ * prims.sum claimed by nvFuser at thunder/executors/nvfuserex_impl.py:2112-2200).
+ *   out[c] = round_T(sum_r f32(x[r, c]))     x: [rows, hidden] of `dtype`, out: [hidden] of `dtype`
+ * scratch: b200k_bias_act_bwd_scratch_bytes(rows, hidden) bytes, contents ignored / unspecified.
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_colsum(const void* x, void* out, void* scratch, int64_t scratch_bytes, int64_t rows, int64_t hidden,
+                           int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Generic pointwise region — SURVEY §8 rows a3/a4.  Executes a fused region made only of elementwise

@@ -41,13 +41,14 @@ EXPORTS: dict[str, tuple] = {
     "b200k_cross_entropy_bwd": (c_int, [c_void_p] * 7 + [c_int64, c_int64, c_int64, c_int, c_int, c_void_p]),
     "b200k_qkv_rope_fwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200k_qkv_rope_bwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
-    "b200k_bias_act_fwd": (c_int, [c_void_p] * 3 + [c_int64, c_int64, c_int, c_int, c_void_p]),
+    "b200k_bias_act_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int64, c_int, c_int, c_void_p]),
     "b200k_bias_act_bwd_scratch_bytes": (c_int64, [c_int64, c_int64]),
     "b200k_bias_act_bwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_int64, c_int, c_int, c_void_p]),
+    "b200k_colsum": (c_int, [c_void_p] * 3 + [c_int64, c_int64, c_int64, c_int, c_void_p]),
     "b200k_pointwise": (c_int, [c_void_p, c_void_p]),
 }
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 _lock = threading.Lock()
 _lib = None

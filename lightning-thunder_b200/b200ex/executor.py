@@ -158,7 +158,7 @@ class B200Executor(FusionExecutor):
             flat: list[BoundSymbol] = []
             for b in bsyms:
                 flat.extend(self.flatten(b))
-            return all(b.sym.id in _MACRO_IMPL or b.sym.id in _PW_OPNAME for b in flat)
+            return all(b.sym.id in _MACRO_IMPL or b.sym.id in _PW_OPNAME or b.sym.id == PrimIDs.SUM for b in flat)
         except AssertionError:
             return False
 
@@ -268,6 +268,19 @@ def _broadcast_check(a, shape, broadcast_dimensions) -> bool:
         and list(broadcast_dimensions) == sorted(broadcast_dimensions)
     )
 
+
+def _sum_check(a, dims) -> bool:
+    """`sum` over all leading dims of a >= 2-D CUDA float tensor (bias / scale gradients): the column reduction
+    b200k_colsum implements.  Other reductions stay with the torch executor."""
+    if not _is_cuda_float(a) or a.ndim < 2:
+        return False
+    try:
+        return tuple(sorted(int(d) % a.ndim for d in dims)) == tuple(range(a.ndim - 1))
+    except TypeError:
+        return False
+
+
+ex.register_supported(PrimIDs.SUM, _sum_check)
 
 for _pid in _PW_OPNAME:
     if _pid is PrimIDs.CONVERT_ELEMENT_TYPE:
@@ -646,6 +659,9 @@ class B200Region:
         absorbed: set[int] = set()
         macro_steps: dict[int, tuple] = {}  # id(bsym) -> (step, input names, output names)
         for b in live:
+            if b.sym.id == PrimIDs.SUM:
+                macro_steps[id(b)] = self._colsum_step(b, prod, consumers, region_outs, absorbed)
+                continue
             if b.sym.id not in _MACRO_IMPL:
                 continue
             fused = self._try_residual_fusion(b, prod, consumers, region_outs, absorbed)
@@ -659,7 +675,7 @@ class B200Region:
             # wave of pointwise work: every node whose inputs are available or produced inside the wave
             wave, wave_out = [], set()
             for b in remaining:
-                if b.sym.id in _MACRO_IMPL:
+                if id(b) in macro_steps:
                     continue
                 if all(n in available or n in wave_out for n in self._arg_names(b)):
                     wave.append(b)
@@ -669,7 +685,7 @@ class B200Region:
                 later = [b for b in remaining if id(b) not in wave_ids]
                 needed = set(region_outs)
                 for b in later:
-                    if b.sym.id not in _MACRO_IMPL:
+                    if id(b) not in macro_steps:
                         needed.update(self._arg_names(b))
                 for _, ins, _ in macro_steps.values():
                     needed.update(ins)
@@ -678,7 +694,7 @@ class B200Region:
                 remaining = later
                 progressed = True
             for b in list(remaining):
-                if b.sym.id in _MACRO_IMPL:
+                if id(b) in macro_steps:
                     step, ins, outs = macro_steps[id(b)]
                     if all(n in available for n in ins):
                         steps.append(step)
@@ -707,6 +723,34 @@ class B200Region:
 
         ins = [n for n, _ in arg_spec if n is not None] + [n for n, _ in kw_spec.values() if n is not None]
         return _Step(b.sym.name, run), ins, [n for n in out_names if n is not None]
+
+    # ---- column sums ----------------------------------------------------------------------------------------
+    def _colsum_step(self, b: BoundSymbol, prod, consumers, region_outs, absorbed: set):
+        """prims.sum over the leading dims.  ltorch.sum of a 16-bit tensor is convert -> sum -> convert; when that
+        is the shape here the reduction reads the 16-bit tensor directly (fp32 accumulate, one rounding — what
+        torch.sum does) and the two converts are absorbed.  A bias-gradient already produced by the native
+        bias+activation backward of the same region is reused instead of being recomputed."""
+        src = b.args[0]
+        src_name = self._resolve(src.name)
+        out = b.output
+        out_name = out.name
+        up = prod.get(src_name)
+        down = self._single_consumer(out.name, consumers, region_outs)
+        if (
+            up is not None and up.sym.id == PrimIDs.CONVERT_ELEMENT_TYPE and isinstance(up.args[0], TensorProxy)
+            and _tdtype(up.args[0].dtype) in (torch.bfloat16, torch.float16) and _tdtype(src.dtype) is torch.float32
+            and down is not None and down.sym.id == PrimIDs.CONVERT_ELEMENT_TYPE and _tdtype(down.output.dtype) is _tdtype(up.args[0].dtype)
+        ):
+            absorbed.add(id(down))
+            if self._single_consumer(up.output.name, consumers, region_outs) is b:
+                absorbed.add(id(up))
+            src_name, out_name = self._resolve(up.args[0].name), down.output.name
+
+        def run(env):
+            ready = env.pop(("dbias", src_name), None)
+            env[out_name] = ready if ready is not None else ops.colsum(env[src_name])
+
+        return _Step("b200k_colsum", run), [src_name], [out_name]
 
     # ---- residual-add peepholes around RMSNorm (dataflow matches) ----------------------------------------
     @staticmethod
@@ -915,6 +959,31 @@ def _native_for(spec) -> _Step | None:
             env[role_out["out"]] = ops.swiglu_fwd(env[role_in["a"]], env[role_in["b"]]).view(shape)
 
         return _Step("b200k_swiglu_fwd", run)
+    if kind in ("bias_gelu_fwd", "bias_relu_fwd"):
+        act = "gelu" if "gelu" in kind else "relu"
+        want_pre = "pre" in role_out
+
+        def run(env):
+            x = env[role_in["x"]]
+            res = ops.bias_act_fwd(x.reshape(shape) if tuple(x.shape) != tuple(shape) else x, env[role_in["b"]], act, return_pre=want_pre)
+            if want_pre:
+                env[role_out["out"]], env[role_out["pre"]] = res
+            else:
+                env[role_out["out"]] = res
+
+        return _Step(f"b200k_bias_act_fwd[{act}]", run)
+    if kind in ("gelu_bwd", "relu_bwd"):
+        act = "gelu" if "gelu" in kind else "relu"
+
+        def run(env):
+            # `a` is the saved pre-activation; the bias gradient is the column sum of dx, deposited for the region's
+            # b200k_colsum step so that it does not have to re-read dx
+            dx, db = ops.bias_act_bwd(env[role_in["a"]], None, env[role_in["g"]], act, want_dbias=len(shape) >= 2)
+            env[role_out["dx"]] = dx
+            if db is not None:
+                env[("dbias", role_out["dx"])] = db
+
+        return _Step(f"b200k_bias_act_bwd[{act}]", run)
     if kind == "swiglu_bwd":
 
         def run(env):

@@ -15,7 +15,7 @@ from . import _lib
 
 __all__ = [
     "rmsnorm_fwd", "rmsnorm_bwd", "swiglu_fwd", "swiglu_bwd", "cross_entropy_fwd", "cross_entropy_bwd",
-    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "ACT_CODE", "DTYPE_CODE",
+    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "colsum", "ACT_CODE", "DTYPE_CODE",
 ]
 
 DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
@@ -209,35 +209,53 @@ def qkv_rope_bwd(dq, dk, dv, cos, sin, n_head: int, n_query_groups: int, head_si
 ACT_CODE = {"none": 0, "relu": 1, "gelu": 2}
 
 
-def bias_act_fwd(x, bias, act: str):
-    """act(x + bias) — see b200k_bias_act_fwd."""
+def bias_act_fwd(x, bias, act: str, return_pre: bool = False):
+    """act(x + bias) — see b200k_bias_act_fwd.  With return_pre also returns the rounded pre-activation x + bias."""
     dev = _require_cuda(x, bias)
     shape = x.shape
     x2 = _rows2d(x)
     b = _contig(bias) if bias is not None else None
     out = torch.empty_like(x2)
+    pre = torch.empty_like(x2) if return_pre else None
     rows, hidden = x2.shape
     with torch.cuda.device(dev):
-        rc = _lib.lib().b200k_bias_act_fwd(_ptr(x2), _ptr(b), _ptr(out), rows, hidden, ACT_CODE[act], _code(x), _stream(dev))
+        rc = _lib.lib().b200k_bias_act_fwd(_ptr(x2), _ptr(b), _ptr(out), _ptr(pre), rows, hidden, ACT_CODE[act], _code(x), _stream(dev))
     _lib.check(rc, "b200k_bias_act_fwd")
-    return out.view(shape)
+    return (out.view(shape), pre.view(shape)) if return_pre else out.view(shape)
 
 
-def bias_act_bwd(x, bias, g, act: str):
-    """(dx, dbias) — see b200k_bias_act_bwd.  dbias is None when bias is None."""
+def bias_act_bwd(x, bias, g, act: str, want_dbias: bool | None = None):
+    """(dx, dbias) — see b200k_bias_act_bwd.  ``x`` is the input when ``bias`` is given, the saved pre-activation when
+    ``bias`` is None.  dbias (column sum of dx) is returned when want_dbias, which defaults to ``bias is not None``."""
     dev = _require_cuda(x, bias, g)
     shape = x.shape
     x2, g2 = _rows2d(x), _rows2d(g)
     b = _contig(bias) if bias is not None else None
     rows, hidden = x2.shape
+    want = (bias is not None) if want_dbias is None else want_dbias
     dx = torch.empty_like(x2)
-    db = torch.empty_like(b) if b is not None else None
+    db = torch.empty(hidden, dtype=x.dtype, device=dev) if want else None
     L = _lib.lib()
     with torch.cuda.device(dev):
-        nbytes = L.b200k_bias_act_bwd_scratch_bytes(rows, hidden) if b is not None else 0
-        scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev) if b is not None else None
+        nbytes = L.b200k_bias_act_bwd_scratch_bytes(rows, hidden) if want else 0
+        scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev) if want else None
         rc = L.b200k_bias_act_bwd(
             _ptr(x2), _ptr(b), _ptr(g2), _ptr(dx), _ptr(db), _ptr(scratch), nbytes, rows, hidden, ACT_CODE[act], _code(x), _stream(dev)
         )
     _lib.check(rc, "b200k_bias_act_bwd")
     return dx.view(shape), db
+
+
+def colsum(x):
+    """Sum over all leading dims: x [..., hidden] -> [hidden] in x's dtype (fp32 accumulation) — see b200k_colsum."""
+    dev = _require_cuda(x)
+    x2 = _rows2d(x)
+    rows, hidden = x2.shape
+    out = torch.empty(hidden, dtype=x.dtype, device=dev)
+    L = _lib.lib()
+    with torch.cuda.device(dev):
+        nbytes = L.b200k_bias_act_bwd_scratch_bytes(rows, hidden)
+        scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+        rc = L.b200k_colsum(_ptr(x2), _ptr(out), _ptr(scratch), nbytes, rows, hidden, _code(x), _stream(dev))
+    _lib.check(rc, "b200k_colsum")
+    return out

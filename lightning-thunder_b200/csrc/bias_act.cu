@@ -5,6 +5,8 @@
 // registers and the backward can keep fp32 partial column sums of dx per thread (dbias), written as
 // one partial row per CTA and folded by colsum_finalize (deterministic, no atomics).
 // act: 0 = none (bias add only), 1 = relu, 2 = gelu (erf form).
+#include <type_traits>
+
 #include "common.cuh"
 #include "reduce.cuh"
 
@@ -111,10 +113,12 @@ __device__ __forceinline__ void act_bwd(const float* a, const float* g, float* d
 }
 
 // grid = (row parts, column tiles); column tile = blockDim.x * kBaVpl vectors.
-template <typename T, int kAct, bool kHasBias, bool kBwd>
+// kAccum: keep fp32 column sums of the (rounded) backward result for dbias; kStore: write `out`;
+// pre_out (forward, nullable): also write the rounded pre-activation a = x + bias, which is what autodiff saves.
+template <typename T, int kAct, bool kHasBias, bool kBwd, bool kAccum, bool kStore = true>
 __global__ void __launch_bounds__(kBaThreads)
 bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __restrict__ g, T* __restrict__ out,
-                float* __restrict__ partial, int64_t rows, int nvec) {
+                T* __restrict__ pre_out, float* __restrict__ partial, int64_t rows, int nvec) {
     using V = Vec<T>;
     constexpr int kE = V::kElems;
     const int tid = threadIdx.x, nthr = blockDim.x;
@@ -155,7 +159,7 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
                     float gf[kE];
                     V::unpack(gv[i], gf);
                     act_bwd<T, kAct>(a, gf, o, kE);
-                    if constexpr (kHasBias) {
+                    if constexpr (kAccum) {
 #pragma unroll
                         for (int e = 0; e < kE; e += 2) {
                             float d0 = o[e], d1 = o[e + 1];
@@ -165,15 +169,16 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
                         }
                     }
                 } else {
+                    if (pre_out != nullptr) st_stream(reinterpret_cast<uint4*>(pre_out) + row * nvec + v, V::pack(a));
                     act_fwd<T, kAct>(a, kE);
 #pragma unroll
                     for (int e = 0; e < kE; ++e) o[e] = a[e];
                 }
-                st_stream(reinterpret_cast<uint4*>(out) + row * nvec + v, V::pack(o));
+                if constexpr (kStore) st_stream(reinterpret_cast<uint4*>(out) + row * nvec + v, V::pack(o));
             }
         }
     }
-    if constexpr (kBwd && kHasBias) {
+    if constexpr (kBwd && kAccum) {
         float* prow = partial + static_cast<int64_t>(blockIdx.x) * nvec * kE;
 #pragma unroll
         for (int i = 0; i < kBaVpl; ++i) {
@@ -193,7 +198,7 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
 template <typename T, bool kBwd>
 __global__ void __launch_bounds__(256)
 bias_act_generic_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __restrict__ g, T* __restrict__ out,
-                        T* __restrict__ dbias, int64_t rows, int64_t hidden, int act) {
+                        T* __restrict__ pre_out, T* __restrict__ dbias, int64_t rows, int64_t hidden, int act) {
     using V = Vec<T>;
     const int64_t col = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
     if (col >= hidden) return;
@@ -210,6 +215,7 @@ bias_act_generic_kernel(const T* __restrict__ x, const T* __restrict__ bias, con
             else act_bwd<T, 2>(a, gf, o, 2);
             acc += V::rnd(o[0]);
         } else {
+            if (pre_out != nullptr) V::store1(pre_out, r * hidden + col, a[0]);
             if (act == 1) act_fwd<T, 1>(a, 2);
             else if (act == 2) act_fwd<T, 2>(a, 2);
             o[0] = a[0];
@@ -226,15 +232,15 @@ int row_parts(int64_t rows, int col_tiles) {
 }
 
 template <typename T, bool kBwd>
-int run(const void* x, const void* bias, const void* g, void* out, void* dbias, void* scratch, int64_t scratch_bytes, int64_t rows,
-        int64_t hidden, int act, cudaStream_t st) {
+int run(const void* x, const void* bias, const void* g, void* out, void* pre_out, void* dbias, void* scratch, int64_t scratch_bytes,
+        int64_t rows, int64_t hidden, int act, cudaStream_t st) {
     using V = Vec<T>;
     const bool vec_ok = hidden % V::kElems == 0 && aligned16(x) && aligned16(out) && (bias == nullptr || aligned16(bias)) &&
-                        (!kBwd || aligned16(g));
+                        (!kBwd || aligned16(g)) && (pre_out == nullptr || aligned16(pre_out));
     if (!vec_ok) {
         bias_act_generic_kernel<T, kBwd><<<static_cast<int>((hidden + 255) / 256), 256, 0, st>>>(
-            static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(g), static_cast<T*>(out), static_cast<T*>(dbias),
-            rows, hidden, act);
+            static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(g), static_cast<T*>(out), static_cast<T*>(pre_out),
+            static_cast<T*>(dbias), rows, hidden, act);
         return launch_status();
     }
     const int nvec = static_cast<int>(hidden / V::kElems);
@@ -243,23 +249,56 @@ int run(const void* x, const void* bias, const void* g, void* out, void* dbias, 
     const int per_tile = (nvec + col_tiles - 1) / col_tiles;
     const int threads = ((per_tile + kBaVpl - 1) / kBaVpl + 31) / 32 * 32;
     const int parts = row_parts(rows, col_tiles);
-    const bool need_partial = kBwd && bias != nullptr;
-    if (need_partial && (scratch == nullptr || !aligned16(scratch) || scratch_bytes < static_cast<int64_t>(parts) * hidden * 4))
+    const bool accum = kBwd && dbias != nullptr;
+    if (accum && (scratch == nullptr || !aligned16(scratch) || scratch_bytes < static_cast<int64_t>(parts) * hidden * 4))
         return B200K_ESCRATCH;
     const dim3 grid(parts, col_tiles);
     auto go = [&](auto kernel) {
         kernel<<<grid, threads, 0, st>>>(static_cast<const T*>(x), static_cast<const T*>(bias), static_cast<const T*>(g),
-                                           static_cast<T*>(out), static_cast<float*>(scratch), rows, nvec);
+                                        static_cast<T*>(out), static_cast<T*>(pre_out), static_cast<float*>(scratch), rows, nvec);
         return launch_status();
     };
+    auto pick = [&](auto has_bias, auto acc) {
+        constexpr bool kB = decltype(has_bias)::value, kA = decltype(acc)::value;
+        return act == 0 ? go(bias_act_kernel<T, 0, kB, kBwd, kA>) : act == 1 ? go(bias_act_kernel<T, 1, kB, kBwd, kA>) : go(bias_act_kernel<T, 2, kB, kBwd, kA>);
+    };
     int rc;
-    if (bias != nullptr) {
-        rc = act == 0 ? go(bias_act_kernel<T, 0, true, kBwd>) : act == 1 ? go(bias_act_kernel<T, 1, true, kBwd>) : go(bias_act_kernel<T, 2, true, kBwd>);
-    } else {
-        rc = act == 0 ? go(bias_act_kernel<T, 0, false, kBwd>) : act == 1 ? go(bias_act_kernel<T, 1, false, kBwd>) : go(bias_act_kernel<T, 2, false, kBwd>);
-    }
-    if (rc != 0 || !need_partial) return rc;
+    if (bias != nullptr) rc = accum ? pick(std::true_type{}, std::true_type{}) : pick(std::true_type{}, std::false_type{});
+    else rc = accum ? pick(std::false_type{}, std::true_type{}) : pick(std::false_type{}, std::false_type{});
+    if (rc != 0 || !accum) return rc;
     return launch_colsum_finalize<T>(scratch, dbias, parts, hidden, st);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_generic_kernel(const T* __restrict__ x, T* __restrict__ out, int64_t rows, int64_t hidden) {
+    const int64_t col = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (col >= hidden) return;
+    float acc = 0.f;
+    for (int64_t r = 0; r < rows; ++r) acc += Vec<T>::load1(x, r * hidden + col);
+    Vec<T>::store1(out, col, acc);
+}
+
+// Column sum of a [rows, hidden] tensor: out[c] = round_T(sum_r f32(x[r, c])) — the reduction a bias gradient or any
+// `sum` over the leading dims of a region output needs.  Same kernel as the bias backward with the activation and
+// the dx store compiled out: one streaming read, fp32 partials per CTA, deterministic fold.
+template <typename T>
+int run_colsum(const void* x, void* out, void* scratch, int64_t scratch_bytes, int64_t rows, int64_t hidden, cudaStream_t st) {
+    using V = Vec<T>;
+    const bool vec_ok = hidden % V::kElems == 0 && aligned16(x);
+    if (!vec_ok) {
+        colsum_generic_kernel<T><<<static_cast<int>((hidden + 255) / 256), 256, 0, st>>>(static_cast<const T*>(x), static_cast<T*>(out), rows, hidden);
+        return launch_status();
+    }
+    const int nvec = static_cast<int>(hidden / V::kElems);
+    const int col_tiles = (nvec + kBaThreads * kBaVpl - 1) / (kBaThreads * kBaVpl);
+    const int per_tile = (nvec + col_tiles - 1) / col_tiles;
+    const int threads = ((per_tile + kBaVpl - 1) / kBaVpl + 31) / 32 * 32;
+    const int parts = row_parts(rows, col_tiles);
+    if (scratch == nullptr || !aligned16(scratch) || scratch_bytes < static_cast<int64_t>(parts) * hidden * 4) return B200K_ESCRATCH;
+    bias_act_kernel<T, 0, false, true, true, false><<<dim3(parts, col_tiles), threads, 0, st>>>(
+        static_cast<const T*>(x), nullptr, static_cast<const T*>(x), nullptr, nullptr, static_cast<float*>(scratch), rows, nvec);
+    if (int rc = launch_status()) return rc;
+    return launch_colsum_finalize<T>(scratch, out, parts, hidden, st);
 }
 
 }  // namespace
@@ -274,16 +313,16 @@ extern "C" int64_t b200k_bias_act_bwd_scratch_bytes(int64_t rows, int64_t hidden
     return parts * hidden * 4;
 }
 
-extern "C" int b200k_bias_act_fwd(const void* x, const void* bias, void* out, int64_t rows, int64_t hidden, int act, int dtype,
-                                  void* stream) {
+extern "C" int b200k_bias_act_fwd(const void* x, const void* bias, void* out, void* pre_out, int64_t rows, int64_t hidden, int act,
+                                  int dtype, void* stream) {
     if (rows < 0 || hidden <= 0 || act < 0 || act > 2) return B200K_EINVAL;
     if (rows == 0) return 0;
     if (x == nullptr || out == nullptr) return B200K_EINVAL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     switch (dtype) {
-        case B200K_F32: return run<float, false>(x, bias, nullptr, out, nullptr, nullptr, 0, rows, hidden, act, st);
-        case B200K_BF16: return run<__nv_bfloat16, false>(x, bias, nullptr, out, nullptr, nullptr, 0, rows, hidden, act, st);
-        case B200K_F16: return run<__half, false>(x, bias, nullptr, out, nullptr, nullptr, 0, rows, hidden, act, st);
+        case B200K_F32: return run<float, false>(x, bias, nullptr, out, pre_out, nullptr, nullptr, 0, rows, hidden, act, st);
+        case B200K_BF16: return run<__nv_bfloat16, false>(x, bias, nullptr, out, pre_out, nullptr, nullptr, 0, rows, hidden, act, st);
+        case B200K_F16: return run<__half, false>(x, bias, nullptr, out, pre_out, nullptr, nullptr, 0, rows, hidden, act, st);
         default: return B200K_EDTYPE;
     }
 }
@@ -291,10 +330,9 @@ extern "C" int b200k_bias_act_fwd(const void* x, const void* bias, void* out, in
 extern "C" int b200k_bias_act_bwd(const void* x, const void* bias, const void* g, void* dx, void* dbias, void* scratch,
                                   int64_t scratch_bytes, int64_t rows, int64_t hidden, int act, int dtype, void* stream) {
     if (rows < 0 || hidden <= 0 || act < 0 || act > 2) return B200K_EINVAL;
-    if (bias != nullptr && dbias == nullptr) return B200K_EINVAL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (rows == 0) {
-        if (bias != nullptr) {
+        if (dbias != nullptr) {
             cudaError_t e = cudaMemsetAsync(dbias, 0, static_cast<size_t>(hidden) * (dtype == B200K_F32 ? 4 : 2), st);
             return e == cudaSuccess ? 0 : static_cast<int>(e);
         }
@@ -302,9 +340,26 @@ extern "C" int b200k_bias_act_bwd(const void* x, const void* bias, const void* g
     }
     if (x == nullptr || g == nullptr || dx == nullptr) return B200K_EINVAL;
     switch (dtype) {
-        case B200K_F32: return run<float, true>(x, bias, g, dx, dbias, scratch, scratch_bytes, rows, hidden, act, st);
-        case B200K_BF16: return run<__nv_bfloat16, true>(x, bias, g, dx, dbias, scratch, scratch_bytes, rows, hidden, act, st);
-        case B200K_F16: return run<__half, true>(x, bias, g, dx, dbias, scratch, scratch_bytes, rows, hidden, act, st);
+        case B200K_F32: return run<float, true>(x, bias, g, dx, nullptr, dbias, scratch, scratch_bytes, rows, hidden, act, st);
+        case B200K_BF16: return run<__nv_bfloat16, true>(x, bias, g, dx, nullptr, dbias, scratch, scratch_bytes, rows, hidden, act, st);
+        case B200K_F16: return run<__half, true>(x, bias, g, dx, nullptr, dbias, scratch, scratch_bytes, rows, hidden, act, st);
+        default: return B200K_EDTYPE;
+    }
+}
+
+extern "C" int b200k_colsum(const void* x, void* out, void* scratch, int64_t scratch_bytes, int64_t rows, int64_t hidden, int dtype,
+                            void* stream) {
+    if (rows < 0 || hidden <= 0 || out == nullptr) return B200K_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (rows == 0) {
+        cudaError_t e = cudaMemsetAsync(out, 0, static_cast<size_t>(hidden) * (dtype == B200K_F32 ? 4 : 2), st);
+        return e == cudaSuccess ? 0 : static_cast<int>(e);
+    }
+    if (x == nullptr) return B200K_EINVAL;
+    switch (dtype) {
+        case B200K_F32: return run_colsum<float>(x, out, scratch, scratch_bytes, rows, hidden, st);
+        case B200K_BF16: return run_colsum<__nv_bfloat16>(x, out, scratch, scratch_bytes, rows, hidden, st);
+        case B200K_F16: return run_colsum<__half>(x, out, scratch, scratch_bytes, rows, hidden, st);
         default: return B200K_EDTYPE;
     }
 }

@@ -68,6 +68,31 @@ def test_no_bias_and_identity():
     assert torch.equal(out.cpu(), x + b)
 
 
+def test_saved_preactivation_form_and_colsum():
+    """What the executor's regions use: the forward also returns the rounded pre-activation, the backward takes it
+    instead of (x, bias) and still returns the bias gradient; colsum is the stand-alone column reduction."""
+    from b200ex import ops
+
+    g0 = torch.Generator().manual_seed(9)
+    mk = lambda *s: (torch.randn(*s, generator=g0) * 1.5).to(torch.bfloat16)
+    x, b, g = mk(300, 1024), mk(1024), mk(300, 1024)
+    out, pre = ops.bias_act_fwd(x.to(DEV), b.to(DEV), "gelu", return_pre=True)
+    assert torch.equal(pre.cpu(), x + b) and torch.equal(out.cpu(), ops.bias_act_fwd(x.to(DEV), b.to(DEV), "gelu").cpu())
+    dx1, db1 = ops.bias_act_bwd(x.to(DEV), b.to(DEV), g.to(DEV), "gelu")
+    dx2, db2 = ops.bias_act_bwd(pre, None, g.to(DEV), "gelu", want_dbias=True)
+    assert torch.equal(dx1, dx2) and torch.equal(db1, db2)
+    assert ops.bias_act_bwd(pre, None, g.to(DEV), "gelu")[1] is None
+    cs = ops.colsum(dx1)
+    assert torch.equal(cs, db1)  # same partial-sum tree
+    ref = torch.sum(dx1.cpu(), 0)
+    terms = dx1.cpu().float().abs()
+    assert_parity(cs, ref, what="colsum", ulp_scale=terms.sum(0) * 2.0**-12)
+    for shape, dt in (((7, 5, 96), torch.float32), ((33, 1001), torch.float16), ((2, 8), torch.bfloat16)):
+        t = torch.randn(*shape, generator=g0).to(dt)
+        assert_parity(ops.colsum(t.to(DEV)), t.reshape(-1, shape[-1]).sum(0), what=f"colsum {shape} {dt}",
+                      ulp_scale=t.float().abs().reshape(-1, shape[-1]).sum(0) * (4.0 if dt == torch.float32 else 2.0**-8))
+
+
 def test_nanogpt_mlp_shape():
     """GPT-2 style MLP activation: bf16 [8192 tokens, 3072], gelu(x + bias)."""
     g = torch.Generator().manual_seed(0)

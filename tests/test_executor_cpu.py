@@ -114,13 +114,22 @@ def test_qkv_split_rope_lookaside():
     assert q.shape == (2, 4, 8, 16) and k.shape == (2, 4, 8, 16)
 
 
+def test_bias_activation_regions_route_to_the_native_kernels():
+    for act, fn in (("gelu", lambda x, b: F.gelu(x + b)), ("relu", lambda x, b: F.relu(x + b))):
+        fw, bw = _trace(fn, torch.randn(6, 32).to(torch.bfloat16).requires_grad_(True), torch.randn(32).to(torch.bfloat16).requires_grad_(True))
+        assert [k for _, ks in fusions(fw) for k in ks] == [f"b200k_bias_act_fwd[{act}]"]
+        # dx from the fused backward kernel, the bias gradient from its column sums (no second pass over dx)
+        assert [k for _, ks in fusions(bw) for k in ks] == [f"b200k_bias_act_bwd[{act}]", "b200k_colsum"]
+
+
 def test_generic_pointwise_region_with_broadcast():
     def f(x, b):
-        return F.gelu(x + b)
+        return torch.tanh(x * b) + 0.5 * x
 
     fw, bw = _trace(f, torch.randn(6, 32).to(torch.bfloat16).requires_grad_(True), torch.randn(32).to(torch.bfloat16).requires_grad_(True))
     assert all(k == "b200k_pointwise" for _, ks in fusions(fw) for k in ks) and fusions(fw)
-    assert any("b200k_pointwise" in ks for _, ks in fusions(bw))
+    kinds = [k for _, ks in fusions(bw) for k in ks]
+    assert "b200k_pointwise" in kinds and "b200k_colsum" in kinds  # db = sum over rows is claimed too
 
 
 def test_optimization_fuel():

@@ -101,10 +101,21 @@ def test_qkv_split_rope_function():
     _compare(res, "qkv_split_rope", grad_atol=2.0**-6)
 
 
-def test_bias_gelu_goes_through_the_generic_interpreter():
-    res = _both(lambda x, b: F.gelu(x + b), [_mk(256, 768, seed=12, scale=1.5), _mk(768, seed=13)])
-    assert "b200k_pointwise" in [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
-    _compare(res, "bias_gelu", ulp=lambda b: b.float().abs() * 4 + 2.0)
+@pytest.mark.parametrize("act", ["gelu", "relu"])
+def test_bias_activation(act):
+    fn = (lambda x, b: F.gelu(x + b)) if act == "gelu" else (lambda x, b: F.relu(x + b))
+    res = _both(fn, [_mk(256, 768, seed=12, scale=1.5), _mk(768, seed=13)])
+    jf = res[0][2]
+    assert [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks] == [f"b200k_bias_act_fwd[{act}]"]
+    assert [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks] == [f"b200k_bias_act_bwd[{act}]", "b200k_colsum"]
+    _compare(res, f"bias_{act}", ulp=lambda b: b.float().abs() * 4 + 2.0)
+
+
+def test_tanh_chain_goes_through_the_generic_interpreter_and_colsum():
+    res = _both(lambda x, b: torch.tanh(x * b) + 0.5 * x, [_mk(256, 768, seed=21), _mk(768, seed=22)])
+    kinds = [k for _, ks in fusions(thunder.last_backward_traces(res[0][2])[-1]) for k in ks]
+    assert "b200k_pointwise" in kinds and "b200k_colsum" in kinds
+    _compare(res, "tanh chain", ulp=lambda b: b.float().abs() * 4 + 2.0)
 
 
 def test_generic_pointwise_fp32_with_broadcasts():

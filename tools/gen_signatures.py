@@ -89,6 +89,32 @@ def main():
 
         specs, fw, bw = collect(ctx, (mk(True), mk(True), mk(True), torch.randn(64).to(dt).requires_grad_(True)))
         classify(specs, bw, table)
+    # ---- bias + activation (gelu, relu): forward (x, b -> [pre,] out), backward (saved pre-activation a, g -> dx) ----
+    for act, fn in (("gelu", lambda x, b: F.gelu(x + b)), ("relu", lambda x, b: F.relu(x + b))):
+        for dt in (torch.bfloat16, torch.float16, torch.float32):
+            mkx = lambda grad: torch.randn(6, 32).to(dt).requires_grad_(grad)
+            mkb = lambda grad: torch.randn(32).to(dt).requires_grad_(grad)
+            specs, fw, bw = collect(fn, (mkx(False), mkb(False)))
+            for spec in specs:
+                leaves = [n for n, _ in spec.leaves]
+                if sorted(leaves) == ["b", "x"] and len(spec.outputs) == 1:
+                    table[spec.signature] = (f"bias_{act}_fwd", tuple(leaves), ("out",))
+            specs, fw, bw = collect(fn, (mkx(True), mkb(True)))
+            fw_ret = None
+            for bs in fw.bound_symbols:
+                if bs.sym.name == "python_return":
+                    fw_ret = bs.args[0]["flat_output"][0].name  # the function's result; the other output is the saved pre-activation
+            for spec in specs:
+                leaves = [n for n, _ in spec.leaves]
+                outs = [n for n, _, _ in spec.outputs]
+                if sorted(leaves) == ["b", "x"] and len(outs) == 2 and fw_ret in outs:
+                    table[spec.signature] = (f"bias_{act}_fwd", tuple(leaves), tuple("out" if n == fw_ret else "pre" for n in outs))
+                    pre_name = [n for n in outs if n != fw_ret][0]
+                elif len(leaves) == 2 and len(outs) == 1 and "x" not in leaves and "b" not in leaves:
+                    # backward: one leaf is the saved pre-activation (same proxy name as the forward's extra output)
+                    roles = tuple("a" if n == pre_name else "g" for n in leaves)
+                    if sorted(roles) == ["a", "g"]:
+                        table[spec.signature] = (f"{act}_bwd", roles, ("dx",))
     path = os.path.join(ROOT, "lightning-thunder_b200", "b200ex", "_signatures.py")
     with open(path, "w") as f:
         f.write('"""Generated by tools/gen_signatures.py — do not edit."""\n\nNATIVE_SIGNATURES = {\n')
