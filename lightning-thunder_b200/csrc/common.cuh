@@ -59,6 +59,15 @@ struct Vec<float> {
     }
     __device__ static __forceinline__ float rnd(float x) { return x; }
     __device__ static __forceinline__ void rnd2(float&, float&) {}
+    // float2 views (kElems / 2 pairs) for the packed fp32x2 arithmetic of sm_100 (FMUL2 / FADD2 / FFMA2)
+    __device__ static __forceinline__ void unpack2(const uint4& v, float2* f) {
+        f[0] = make_float2(__uint_as_float(v.x), __uint_as_float(v.y));
+        f[1] = make_float2(__uint_as_float(v.z), __uint_as_float(v.w));
+    }
+    __device__ static __forceinline__ uint4 pack2(const float2* f) {
+        return make_uint4(__float_as_uint(f[0].x), __float_as_uint(f[0].y), __float_as_uint(f[1].x), __float_as_uint(f[1].y));
+    }
+    __device__ static __forceinline__ float2 rnd2f(float2 x) { return x; }
     __device__ static __forceinline__ float load1(const void* p, int64_t i) { return reinterpret_cast<const float*>(p)[i]; }
     __device__ static __forceinline__ void store1(void* p, int64_t i, float x) { reinterpret_cast<float*>(p)[i] = x; }
 };
@@ -92,6 +101,18 @@ struct Vec<__nv_bfloat16> {
         a = __uint_as_float(u << 16);
         b = __uint_as_float(u & 0xffff0000u);
     }
+    __device__ static __forceinline__ float2 word2(uint32_t w) { return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)); }
+    __device__ static __forceinline__ void unpack2(const uint4& v, float2* f) {
+        f[0] = word2(v.x), f[1] = word2(v.y), f[2] = word2(v.z), f[3] = word2(v.w);
+    }
+    __device__ static __forceinline__ uint32_t pack_word(float2 x) {
+        __nv_bfloat162 p = __floats2bfloat162_rn(x.x, x.y);
+        return *reinterpret_cast<uint32_t*>(&p);
+    }
+    __device__ static __forceinline__ uint4 pack2(const float2* f) {
+        return make_uint4(pack_word(f[0]), pack_word(f[1]), pack_word(f[2]), pack_word(f[3]));
+    }
+    __device__ static __forceinline__ float2 rnd2f(float2 x) { return word2(pack_word(x)); }
     __device__ static __forceinline__ float load1(const void* p, int64_t i) {
         return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
     }
@@ -128,6 +149,21 @@ struct Vec<__half> {
         a = r.x;
         b = r.y;
     }
+    __device__ static __forceinline__ void unpack2(const uint4& v, float2* f) {
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) f[i] = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    }
+    __device__ static __forceinline__ uint4 pack2(const float2* f) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            __half2 p = __floats2half2_rn(f[i].x, f[i].y);
+            w[i] = *reinterpret_cast<uint32_t*>(&p);
+        }
+        return make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    __device__ static __forceinline__ float2 rnd2f(float2 x) { return __half22float2(__floats2half2_rn(x.x, x.y)); }
     __device__ static __forceinline__ float load1(const void* p, int64_t i) {
         return __half2float(reinterpret_cast<const __half*>(p)[i]);
     }

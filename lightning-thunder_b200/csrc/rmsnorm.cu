@@ -345,13 +345,16 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
     }
     __syncthreads();
 
-    float wf[kVpl][kE];
-    float dwacc[kVpl][kE];
+    // All arithmetic below is on float2 pairs: sm_100's packed FMUL2 / FADD2 / FFMA2 halve the fp32 instruction
+    // count of this issue-bound kernel, with results identical to the scalar round-to-nearest operations.
+    constexpr int kP = kE / 2;
+    float2 wf[kVpl][kP];
+    float2 dwacc[kVpl][kP];
 #pragma unroll
     for (int i = 0; i < kVpl; ++i) {
-        if constexpr (kHasW) V::unpack(ld_keep(reinterpret_cast<const uint4*>(w) + tid + i * nc), wf[i]);
+        if constexpr (kHasW) V::unpack2(ld_keep(reinterpret_cast<const uint4*>(w) + tid + i * nc), wf[i]);
 #pragma unroll
-        for (int e = 0; e < kE; ++e) dwacc[i][e] = 0.f;
+        for (int e = 0; e < kP; ++e) dwacc[i][e] = make_float2(0.f, 0.f);
     }
 
     // Let the dependent dw-reduce grid be scheduled early; it blocks in griddepcontrol.wait until this grid is done.
@@ -387,16 +390,16 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
         float c[kRows];
 #pragma unroll
         for (int r = 0; r < kRows; ++r) {
-            float acc = 0.f;
+            float2 acc = make_float2(0.f, 0.f);
 #pragma unroll
             for (int i = 0; i < kVpl; ++i) {
-                float dyf[kE], hf[kE];
-                V::unpack(dyv[r][i], dyf);
-                V::unpack(hv[r][i], hf);
+                float2 dyf[kP], hf[kP];
+                V::unpack2(dyv[r][i], dyf);
+                V::unpack2(hv[r][i], hf);
 #pragma unroll
-                for (int e = 0; e < kE; ++e) acc += hf[e] * (kHasW ? wf[i][e] * dyf[e] : dyf[e]);
+                for (int e = 0; e < kP; ++e) acc = __ffma2_rn(hf[e], kHasW ? __fmul2_rn(wf[i][e], dyf[e]) : dyf[e], acc);
             }
-            c[r] = warp_reduce(acc, SumOp{});
+            c[r] = warp_reduce(acc.x + acc.y, SumOp{});
         }
         if (ncw > 1) {
             float* rb = red + parity * (kRows * 32);
@@ -433,46 +436,35 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
             const float t3 = (-0.5f * c[r]) * (rstd_r * rstd_r * rstd_r);
             // t3 / hidden; a multiply by the exact reciprocal when hidden is a power of two (bit-identical).
             const float sc = inv_hidden_exact != 0.f ? t3 * inv_hidden_exact : t3 / hidden_f;
+            const float2 rstd2 = make_float2(rstd_r, rstd_r), sc2 = make_float2(sc, sc);
 #pragma unroll
             for (int i = 0; i < kVpl; ++i) {
-                float dyf[kE], hf[kE], o[kE], dwt[kE];
-                V::unpack(dyv[r][i], dyf);
-                V::unpack(hv[r][i], hf);
+                float2 dyf[kP], hf[kP], o[kP];
+                V::unpack2(dyv[r][i], dyf);
+                V::unpack2(hv[r][i], hf);
 #pragma unroll
-                for (int e = 0; e < kE; ++e) {
-                    const float gg = kHasW ? wf[i][e] * dyf[e] : dyf[e];
-                    const float hs = hf[e] * sc;
-                    o[e] = rstd_r * gg;
-                    o[e + 0] = kHasDhIn && kIsF32 ? o[e] : (o[e] + hs) + hs;
-                    if constexpr (kHasW) dwt[e] = (hf[e] * rstd_r) * dyf[e];
-                }
-                if constexpr (kHasW) {
-#pragma unroll
-                    for (int e = 0; e < kE; e += 2) {
-                        V::rnd2(dwt[e], dwt[e + 1]);
-                        dwacc[i][e] += dwt[e];
-                        dwacc[i][e + 1] += dwt[e + 1];
-                    }
+                for (int e = 0; e < kP; ++e) {
+                    const float2 gg = kHasW ? __fmul2_rn(wf[i][e], dyf[e]) : dyf[e];
+                    const float2 hs = __fmul2_rn(hf[e], sc2);
+                    o[e] = __fmul2_rn(rstd2, gg);
+                    if constexpr (!(kHasDhIn && kIsF32)) o[e] = __fadd2_rn(__fadd2_rn(o[e], hs), hs);
+                    if constexpr (kHasW) dwacc[i][e] = __fadd2_rn(dwacc[i][e], V::rnd2f(__fmul2_rn(__fmul2_rn(hf[e], rstd2), dyf[e])));
                 }
                 if constexpr (kHasDhIn) {
-                    float df[kE];
-                    V::unpack(div[r][i], df);
-                    if constexpr (kIsF32) {
+                    float2 df[kP];
+                    V::unpack2(div[r][i], df);
 #pragma unroll
-                        for (int e = 0; e < kE; ++e) {
-                            const float hs = hf[e] * sc;
-                            o[e] = ((df[e] + o[e]) + hs) + hs;
-                        }
-                    } else {
-#pragma unroll
-                        for (int e = 0; e < kE; e += 2) {
-                            V::rnd2(o[e], o[e + 1]);
-                            o[e] += df[e];
-                            o[e + 1] += df[e + 1];
+                    for (int e = 0; e < kP; ++e) {
+                        if constexpr (kIsF32) {
+                            // fp32 has no rounding boundary: the reference accumulates dh_in first
+                            const float2 hs = __fmul2_rn(hf[e], sc2);
+                            o[e] = __fadd2_rn(__fadd2_rn(__fadd2_rn(df[e], o[e]), hs), hs);
+                        } else {
+                            o[e] = __fadd2_rn(df[e], V::rnd2f(o[e]));
                         }
                     }
                 }
-                st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, V::pack(o));
+                st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, V::pack2(o));
             }
         }
     }
@@ -485,7 +477,7 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
 #pragma unroll
             for (int q = 0; q < kE / 4; ++q) {
                 reinterpret_cast<float4*>(prow + static_cast<int64_t>(v) * kE)[q] =
-                    make_float4(dwacc[i][4 * q], dwacc[i][4 * q + 1], dwacc[i][4 * q + 2], dwacc[i][4 * q + 3]);
+                    make_float4(dwacc[i][2 * q].x, dwacc[i][2 * q].y, dwacc[i][2 * q + 1].x, dwacc[i][2 * q + 1].y);
             }
         }
     }

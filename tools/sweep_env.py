@@ -8,7 +8,7 @@ for cfg in sys.argv[1:]:
     for kv in filter(None, cfg.split(",")):
         k, v = kv.split("=")
         env[k] = v
-    p = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--no-cpu-baseline", "--no-e2e", "--steps", "500", "--warmup", "20"],
+    p = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--no-cpu-baseline", "--no-e2e", "--no-train-step", "--steps", "500", "--warmup", "20"],
                        env=env, capture_output=True, text=True)
     try:
         d = json.loads(p.stdout.strip().splitlines()[-1])
