@@ -19,56 +19,75 @@ constexpr int kBaRowParts = 4;  // CTAs per SM along rows (sizes the scratch)
 constexpr float kInvSqrt2 = 0.70710678118654752440f;
 constexpr float kTwoOverSqrtPi = 1.1283791670955126f;
 
+// All activation math runs on float2 pairs (sm_100 packed FMUL2 / FADD2 / FFMA2: half the fp32 instructions of
+// this ALU-bound chain, results identical to scalar round-to-nearest ops).
+__device__ __forceinline__ float2 f2(float x) { return make_float2(x, x); }
+__device__ __forceinline__ float hw_rcp(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float hw_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // erf for bf16 storage: Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, far below half a bf16 ulp of a value in
 // [-1, 1]) on the hardware exp2 / reciprocal units; fp16 and fp32 storage keep erff.
 template <bool kFast>
-__device__ __forceinline__ float erf_f32(float x) {
+__device__ __forceinline__ float2 erf2(float2 x) {
     if constexpr (kFast) {
-        const float ax = fabsf(x);
-        float t, e;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
-        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(ax * ax * -1.4426950408889634f));
-        float p = fmaf(1.061405429f, t, -1.453152027f);
-        p = fmaf(p, t, 1.421413741f);
-        p = fmaf(p, t, -0.284496736f);
-        p = fmaf(p, t, 0.254829592f);
-        const float r = 1.0f - p * t * e;
-        return copysignf(r, x);
+        const float2 ax = make_float2(fabsf(x.x), fabsf(x.y));
+        const float2 d = __ffma2_rn(f2(0.3275911f), ax, f2(1.0f));
+        const float2 t = make_float2(hw_rcp(d.x), hw_rcp(d.y));
+        const float2 q = __fmul2_rn(__fmul2_rn(ax, ax), f2(-1.4426950408889634f));
+        const float2 e = make_float2(hw_ex2(q.x), hw_ex2(q.y));
+        float2 p = __ffma2_rn(f2(1.061405429f), t, f2(-1.453152027f));
+        p = __ffma2_rn(p, t, f2(1.421413741f));
+        p = __ffma2_rn(p, t, f2(-0.284496736f));
+        p = __ffma2_rn(p, t, f2(0.254829592f));
+        const float2 r = __ffma2_rn(__fmul2_rn(p, t), make_float2(-e.x, -e.y), f2(1.0f));
+        return make_float2(copysignf(r.x, x.x), copysignf(r.y, x.y));
     } else {
-        return erff(x);
+        return make_float2(erff(x.x), erff(x.y));
     }
 }
+// 2/sqrt(pi) * exp(-z^2)
 template <bool kFast>
-__device__ __forceinline__ float exp_negsq(float z) {
+__device__ __forceinline__ float2 gauss2(float2 z) {
     if constexpr (kFast) {
-        float e;
-        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
-        return e;
+        const float2 q = __fmul2_rn(__fmul2_rn(z, z), f2(-1.4426950408889634f));
+        return __fmul2_rn(f2(kTwoOverSqrtPi), make_float2(hw_ex2(q.x), hw_ex2(q.y)));
     } else {
-        return expf(-(z * z));
+        return make_float2(kTwoOverSqrtPi * expf(-(z.x * z.x)), kTwoOverSqrtPi * expf(-(z.y * z.y)));
     }
+}
+
+// gelu(a) with one storage rounding per ltorch op: a * rnd(0.5 + rnd(0.5 * rnd(erf(rnd(a / sqrt2)))))
+template <typename T>
+__device__ __forceinline__ float2 gelu_cdf2(float2 a, float2& z_out) {
+    using V = Vec<T>;
+    constexpr bool kFast = V::kDtype == B200K_BF16;
+    const float2 z = V::rnd2f(__fmul2_rn(a, f2(kInvSqrt2)));
+    z_out = z;
+    float2 c = V::rnd2f(erf2<kFast>(z));
+    c = V::rnd2f(__fmul2_rn(c, f2(0.5f)));
+    return V::rnd2f(__fadd2_rn(c, f2(0.5f)));
 }
 
 template <typename T, int kAct>
 __device__ __forceinline__ void act_fwd(float* a /* rounded pre-activation, in/out */, int n) {
-    using V = Vec<T>;
 #pragma unroll
     for (int e = 0; e < n; e += 2) {
-        float a0 = a[e], a1 = a[e + 1];
+        const float2 v = make_float2(a[e], a[e + 1]);
         if constexpr (kAct == 1) {
-            a[e] = a0 > 0.f ? a0 : 0.f;
-            a[e + 1] = a1 > 0.f ? a1 : 0.f;
+            a[e] = v.x > 0.f ? v.x : 0.f;
+            a[e + 1] = v.y > 0.f ? v.y : 0.f;
         } else if constexpr (kAct == 2) {
-            float z0 = a0 * kInvSqrt2, z1 = a1 * kInvSqrt2;
-            V::rnd2(z0, z1);
-            float r0 = erf_f32<V::kDtype == B200K_BF16>(z0), r1 = erf_f32<V::kDtype == B200K_BF16>(z1);
-            V::rnd2(r0, r1);
-            r0 *= 0.5f, r1 *= 0.5f;
-            V::rnd2(r0, r1);
-            r0 += 0.5f, r1 += 0.5f;
-            V::rnd2(r0, r1);
-            a[e] = a0 * r0;
-            a[e + 1] = a1 * r1;
+            float2 z;
+            const float2 o = __fmul2_rn(v, gelu_cdf2<T>(v, z));
+            a[e] = o.x, a[e + 1] = o.y;
         }
     }
 }
@@ -76,43 +95,29 @@ __device__ __forceinline__ void act_fwd(float* a /* rounded pre-activation, in/o
 template <typename T, int kAct>
 __device__ __forceinline__ void act_bwd(const float* a, const float* g, float* dx, int n) {
     using V = Vec<T>;
-    constexpr bool kIsF32 = V::kDtype == B200K_F32;
-    constexpr bool kIsBF16 = V::kDtype == B200K_BF16;
+    constexpr bool kFast = V::kDtype == B200K_BF16;
 #pragma unroll
     for (int e = 0; e < n; e += 2) {
-        const float a0 = a[e], a1 = a[e + 1], g0 = g[e], g1 = g[e + 1];
+        const float2 av = make_float2(a[e], a[e + 1]), gv = make_float2(g[e], g[e + 1]);
         if constexpr (kAct == 0) {
-            dx[e] = g0, dx[e + 1] = g1;
+            dx[e] = gv.x, dx[e + 1] = gv.y;
         } else if constexpr (kAct == 1) {
-            dx[e] = a0 > 0.f ? g0 : 0.f;
-            dx[e + 1] = a1 > 0.f ? g1 : 0.f;
+            dx[e] = av.x > 0.f ? gv.x : 0.f;
+            dx[e + 1] = av.y > 0.f ? gv.y : 0.f;
         } else {
-            float z0 = a0 * kInvSqrt2, z1 = a1 * kInvSqrt2;
-            V::rnd2(z0, z1);
-            float c0 = erf_f32<kIsBF16>(z0), c1 = erf_f32<kIsBF16>(z1);
-            V::rnd2(c0, c1);
-            c0 *= 0.5f, c1 *= 0.5f;
-            V::rnd2(c0, c1);
-            c0 += 0.5f, c1 += 0.5f;
-            V::rnd2(c0, c1);  // cdf
-            float p0 = c0 * g0, p1 = c1 * g1;
-            V::rnd2(p0, p1);
-            float q0 = a0 * g0, q1 = a1 * g1;
-            V::rnd2(q0, q1);
-            q0 *= 0.5f, q1 *= 0.5f;
-            V::rnd2(q0, q1);
-            const float pdf0 = kTwoOverSqrtPi * exp_negsq<kIsBF16>(z0), pdf1 = kTwoOverSqrtPi * exp_negsq<kIsBF16>(z1);
-            float r0 = pdf0 * q0, r1 = pdf1 * q1;
-            V::rnd2(r0, r1);
-            r0 *= kInvSqrt2, r1 *= kInvSqrt2;
-            if constexpr (!kIsF32) V::rnd2(r0, r1);
-            dx[e] = p0 + r0;
-            dx[e + 1] = p1 + r1;
+            float2 z;
+            const float2 cdf = gelu_cdf2<T>(av, z);
+            const float2 p = V::rnd2f(__fmul2_rn(cdf, gv));                      // cdf * g
+            float2 q = V::rnd2f(__fmul2_rn(av, gv));                             // a * g
+            q = V::rnd2f(__fmul2_rn(q, f2(0.5f)));
+            float2 r = V::rnd2f(__fmul2_rn(gauss2<kFast>(z), q));                // pdf term
+            r = V::rnd2f(__fmul2_rn(r, f2(kInvSqrt2)));
+            const float2 o = __fadd2_rn(p, r);
+            dx[e] = o.x, dx[e + 1] = o.y;
         }
     }
 }
 
-// grid = (row parts, column tiles); column tile = blockDim.x * kBaVpl vectors.
 // kAccum: keep fp32 column sums of the (rounded) backward result for dbias; kStore: write `out`;
 // pre_out (forward, nullable): also write the rounded pre-activation a = x + bias, which is what autodiff saves.
 template <typename T, int kAct, bool kHasBias, bool kBwd, bool kAccum, bool kStore = true>
@@ -131,16 +136,22 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
         for (int e = 0; e < kE; ++e) bf[i][e] = 0.f, acc[i][e] = 0.f;
         if (kHasBias && v < nvec) V::unpack(ld_keep(reinterpret_cast<const uint4*>(bias) + v), bf[i]);
     }
-    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
-        uint4 xv[kBaVpl], gv[kBaVpl];
+    // software pipeline: the next row's vectors are requested before the current row's ALU chain starts, so
+    // every thread always has loads in flight
+    uint4 xv[kBaVpl], gv[kBaVpl], xn[kBaVpl], gn[kBaVpl];
+    auto fetch = [&](int64_t row, uint4* xd, uint4* gd) {
 #pragma unroll
         for (int i = 0; i < kBaVpl; ++i) {
             const int v = v0 + i * nthr;
-            if (v < nvec) {
-                xv[i] = ld_stream(reinterpret_cast<const uint4*>(x) + row * nvec + v);
-                if constexpr (kBwd) gv[i] = ld_stream(reinterpret_cast<const uint4*>(g) + row * nvec + v);
+            if (row < rows && v < nvec) {
+                xd[i] = ld_stream(reinterpret_cast<const uint4*>(x) + row * nvec + v);
+                if constexpr (kBwd) gd[i] = ld_stream(reinterpret_cast<const uint4*>(g) + row * nvec + v);
             }
         }
+    };
+    fetch(blockIdx.x, xv, gv);
+    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+        fetch(row + gridDim.x, xn, gn);
 #pragma unroll
         for (int i = 0; i < kBaVpl; ++i) {
             const int v = v0 + i * nthr;
@@ -176,6 +187,11 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
                 }
                 if constexpr (kStore) st_stream(reinterpret_cast<uint4*>(out) + row * nvec + v, V::pack(o));
             }
+        }
+#pragma unroll
+        for (int i = 0; i < kBaVpl; ++i) {
+            xv[i] = xn[i];
+            if constexpr (kBwd) gv[i] = gn[i];
         }
     }
     if constexpr (kBwd && kAccum) {

@@ -12,8 +12,12 @@
 namespace b200k {
 namespace {
 
-constexpr int kCeThreads = 512;
-constexpr int kCeUnroll = 4;
+// forward: 256 threads x 8 loads in flight (latency-bound on the single pass over a 256 KB row);
+// backward: 512 x 4 (write-heavy, more CTAs in flight does not help)
+constexpr int kCeThreads = 256;
+constexpr int kCeUnroll = 8;
+constexpr int kCeBwdThreads = 512;
+constexpr int kCeBwdUnroll = 4;
 constexpr float kLog2e = 1.4426950408889634f;
 
 // 2^x, hardware approximation (2 ulp), flushing results below 2^-126 to zero: such terms cannot change an fp32 sum.
@@ -157,7 +161,7 @@ ce_finalize_kernel(const float* __restrict__ row_nll, const int64_t* __restrict_
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kCeThreads)
+__global__ void __launch_bounds__(kCeBwdThreads)
 ce_bwd_kernel(const T* __restrict__ g, const T* __restrict__ logits, const int64_t* __restrict__ target,
               const float* __restrict__ row_max, const float* __restrict__ row_logsum, const int64_t* __restrict__ n_valid,
               T* __restrict__ dlogits, int64_t rows, int64_t vocab, int64_t ignore_index, int reduction, int vec_ok) {
@@ -182,21 +186,21 @@ ce_bwd_kernel(const T* __restrict__ g, const T* __restrict__ logits, const int64
         if (!valid) {
             // ignored row: gradient is exactly zero
             const uint4 z = make_uint4(0, 0, 0, 0);
-            for (int64_t i = tid; i < nvec; i += kCeThreads) st_stream(reinterpret_cast<uint4*>(dx) + i, z);
-            for (int64_t j = nvec * kE + tid; j < vocab; j += kCeThreads) V::store1(dx, j, 0.f);
+            for (int64_t i = tid; i < nvec; i += kCeBwdThreads) st_stream(reinterpret_cast<uint4*>(dx) + i, z);
+            for (int64_t j = nvec * kE + tid; j < vocab; j += kCeBwdThreads) V::store1(dx, j, 0.f);
             continue;
         }
         const int64_t tvec = tg / kE;
-        for (int64_t base = tid; base < nvec; base += kCeThreads * kCeUnroll) {
-            uint4 v[kCeUnroll];
+        for (int64_t base = tid; base < nvec; base += kCeBwdThreads * kCeBwdUnroll) {
+            uint4 v[kCeBwdUnroll];
 #pragma unroll
-            for (int u = 0; u < kCeUnroll; ++u) {
-                const int64_t i = base + static_cast<int64_t>(u) * kCeThreads;
+            for (int u = 0; u < kCeBwdUnroll; ++u) {
+                const int64_t i = base + static_cast<int64_t>(u) * kCeBwdThreads;
                 if (i < nvec) v[u] = ld_stream(reinterpret_cast<const uint4*>(x) + i);
             }
 #pragma unroll
-            for (int u = 0; u < kCeUnroll; ++u) {
-                const int64_t i = base + static_cast<int64_t>(u) * kCeThreads;
+            for (int u = 0; u < kCeBwdUnroll; ++u) {
+                const int64_t i = base + static_cast<int64_t>(u) * kCeBwdThreads;
                 if (i < nvec) {
                     float f[kE], o[kE];
                     V::unpack(v[u], f);
@@ -217,7 +221,7 @@ ce_bwd_kernel(const T* __restrict__ g, const T* __restrict__ logits, const int64
                 }
             }
         }
-        for (int64_t j = nvec * kE + tid; j < vocab; j += kCeThreads) {
+        for (int64_t j = nvec * kE + tid; j < vocab; j += kCeBwdThreads) {
             const float lp = V::rnd((V::load1(x, j) - m) - ls);
             float o = -(exp2f(lp * kLog2e) * d);
             if (j == tg) o = d + o;
@@ -252,7 +256,7 @@ int run_bwd(const void* g, const void* logits, const int64_t* target, const floa
     const int vec_ok = aligned16(logits) && aligned16(dlogits) && vocab % kE == 0;
     const int64_t cap = static_cast<int64_t>(sm_count()) * 4;
     const int grid = static_cast<int>(rows < cap ? rows : cap);
-    ce_bwd_kernel<T><<<grid, kCeThreads, 0, st>>>(static_cast<const T*>(g), static_cast<const T*>(logits), target, row_max, row_logsum,
+    ce_bwd_kernel<T><<<grid, kCeBwdThreads, 0, st>>>(static_cast<const T*>(g), static_cast<const T*>(logits), target, row_max, row_logsum,
                                                   n_valid, static_cast<T*>(dlogits), rows, vocab, ignore_index, reduction, vec_ok);
     return launch_status();
 }
