@@ -165,7 +165,7 @@ class B200Executor(FusionExecutor):
     # -- the pass (nvfuserex_impl.py:836-939) ---------------------------------------------------------
     def fusion_pass(self, trace: TraceCtx) -> TraceCtx:
         start = time.perf_counter_ns()
-        from thunder.executors.data_dependent_partition import Node, fuse_bound_symbols
+        from thunder.executors.data_dependent_partition import Node, consecutive_fusion, dataflow_fusion, fuse_bound_symbols
 
         fusedtrace: TraceCtx = from_trace(trace)
         producers, consumers = utils.producers_and_consumers(trace)
@@ -176,7 +176,16 @@ class B200Executor(FusionExecutor):
             b = n.group_bsyms[0]
             return self.can_fuse(b) and self._has_cuda_tensor(b)
 
-        groups = fuse_bound_symbols(trace, lambda a, b: _can_fuse_node(a) and _can_fuse_node(b))
+        # Partitioning: the reference's `fusion_type` option wins when the user sets it; otherwise b200 defaults to the
+        # dataflow partitioner (data_dependent_partition.py:339-343), which keeps chains that a matmul interleaves
+        # in one region — e.g. the two halves of the SwiGLU backward — so that they reach their native kernel.
+        merge = lambda a, b: _can_fuse_node(a) and _can_fuse_node(b)
+        if get_compile_option("fusion_type", "Choose the type of fusion to use") is not None:
+            groups = fuse_bound_symbols(trace, merge)
+        else:
+            ft = get_compile_option("b200_fusion_type", "Partitioner b200 uses when fusion_type is not given: 'dataflow' (default) or 'consecutive'.") or "dataflow"
+            utils.check(ft in ("dataflow", "consecutive"), lambda: f"Unknown b200_fusion_type: {ft}", exception_type=ValueError)
+            groups = dataflow_fusion(trace, merge) if ft == "dataflow" else consecutive_fusion(trace, merge)
         enable_shape_only = get_compile_option("b200_enable_shape_only_fusion", "Let b200 fuse regions made only of shape operations. Defaults to False.")
         min_region = get_compile_option("b200_min_region_size", "Smallest number of bound symbols b200 turns into a fusion. Defaults to 1.") or 1
 

@@ -162,8 +162,8 @@ def test_shape_only_groups_are_not_fused():
 
 
 def test_llama_block_region_census():
-    """Region census of a Llama-style model: with fusion_type='dataflow' every named family
-    is lowered to its hand-written kernel."""
+    """Region census of a Llama-style model: with b200's default partitioner (dataflow) every
+    named family is lowered to its hand-written kernel."""
     from baseline.llama_model import GPT, build_rope_cache, tiny_config
 
     cfg = tiny_config()
@@ -171,7 +171,7 @@ def test_llama_block_region_census():
     m = GPT(cfg).to(torch.bfloat16)
     cos, sin = build_rope_cache(16, cfg.rope_n_elem, dtype=torch.bfloat16)
     idx, tgt = torch.randint(0, 256, (2, 16)), torch.randint(0, 256, (2, 16))
-    jm = thunder.jit(m, executors=[b200.ex], fusion_type="dataflow")
+    jm = thunder.jit(m, executors=[b200.ex])
     with pytest.raises(RuntimeError, match="CUDA"):
         jm(idx, cos, sin, tgt)
     fk = [k for _, ks in fusions(thunder.last_traces(jm)[-1]) for k in ks]
@@ -184,6 +184,28 @@ def test_llama_block_region_census():
     assert bk.count("b200_qkv_rope_bwd") == L and bk.count("b200k_swiglu_bwd") == L
     assert bk.count("b200_rms_norm_bwd") + bk.count("b200_rms_norm_bwd+residual") == 2 * L + 1
     assert bk.count("b200_cross_entropy_bwd") == 1
+
+
+def test_partitioner_options():
+    """`fusion_type` (the reference's option) wins; otherwise `b200_fusion_type` picks, default dataflow.  With the
+    consecutive partitioner a matmul between the two halves of the SwiGLU backward splits it in two regions."""
+    lin = torch.nn.Linear(16, 16, bias=False).to(torch.bfloat16)
+
+    def f(x, w1, w2):
+        return lin(F.silu(x @ w1) * (x @ w2))
+
+    mk = lambda *s: torch.randn(*s).to(torch.bfloat16).requires_grad_(True)
+    args = (mk(8, 16), mk(16, 16), mk(16, 16))
+
+    def kinds(**opts):
+        _, bw = _trace(f, *args, **opts)
+        return [k for _, ks in fusions(bw) for k in ks]
+
+    assert "b200k_swiglu_bwd" in kinds()
+    assert "b200k_swiglu_bwd" in kinds(fusion_type="dataflow")
+    for opts in ({"fusion_type": "consecutive"}, {"b200_fusion_type": "consecutive"}):
+        ks = kinds(**opts)
+        assert "b200k_swiglu_bwd" not in ks and ks.count("b200k_pointwise") >= 2
 
 
 def test_signature_table_is_current():
