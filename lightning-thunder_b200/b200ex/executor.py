@@ -24,9 +24,7 @@ What it does, mirroring thunder/executors/nvfuserex_impl.py:
 from __future__ import annotations
 
 import os
-import threading
 import time
-from numbers import Number
 from typing import Any, Callable
 
 import torch
@@ -460,10 +458,6 @@ def _qkv_split_rope_like(qkv, cos, sin, n_head, n_query_groups, head_size, rope_
     return _qkv_split_rope_body(ltorch.cat, qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
 
 
-def _kv_heads(n_head, groups):
-    return n_head if (groups != n_head and groups != 1) else groups
-
-
 def _rope_bwd_meta(dq, dk, dv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem):
     B, T = dq.shape[0], dq.shape[2]
     return TensorProxy(like=dq, shape=(B, T, (n_head + 2 * n_query_groups) * head_size))
@@ -568,18 +562,6 @@ _MACRO_IMPL: dict[Any, Callable] = {
 # --------------------------------------------------------------------------------------------------
 # Region lowering and launch (the role of FusionDefinitionWrapper, nvfuserex_impl.py:526-576)
 # --------------------------------------------------------------------------------------------------
-def _descriptor(args) -> tuple:
-    """Cache key of a call: (shape, stride, dtype) per tensor, the value per number — the analogue of
-    to_runtime_descriptors (nvfuserex_impl.py:505-521), needed because proxies carry no strides."""
-    key = []
-    for a in args:
-        if isinstance(a, torch.Tensor):
-            key.append((tuple(a.shape), a.stride(), a.dtype, a.device.index))
-        else:
-            key.append((type(a), a))
-    return tuple(key)
-
-
 class _Step:
     """One launch (or one zero-copy alias) of a lowered region."""
 

@@ -20,7 +20,7 @@ import hashlib
 import itertools
 import struct
 import threading
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 
 import torch
 
@@ -40,7 +40,6 @@ UNARY = {"neg", "abs", "exp", "log", "sqrt", "rsqrt", "reciprocal", "erf", "tanh
 # ops whose fp32 result is exactly representable whenever the operands are: no rounding instruction needed
 EXACT = {"neg", "abs", "where", "mov", "maximum", "minimum", "sign", "gt", "ge", "lt", "le", "eq", "ne", "and", "or", "not",
          "floor", "ceil", "trunc", "round"}
-COMPARE = {"gt", "ge", "lt", "le", "eq", "ne", "and", "or", "not"}
 
 DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2, torch.bool: 3}
 
