@@ -42,6 +42,23 @@ def _require_cuda(*ts) -> torch.device:
     return dev
 
 
+class _NoCtx:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NOCTX = _NoCtx()
+
+
+def _on(dev: torch.device):
+    """Context that makes `dev` current for the launch; free when it already is (the common case: switching
+    devices through torch costs more host time than the launch itself)."""
+    return _NOCTX if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
+
+
 def _ptr(t):
     return None if t is None else t.data_ptr()
 
@@ -68,7 +85,7 @@ def rmsnorm_fwd(x, residual, weight, eps: float):
     y = torch.empty_like(x2)
     h = torch.empty_like(x2) if residual is not None else None
     rstd = torch.empty(rows, dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_rmsnorm_fwd(
             _ptr(x2), _ptr(r2), _ptr(w), _ptr(h), _ptr(y), _ptr(rstd), rows, hidden, float(eps), _code(x), _stream(dev)
         )
@@ -89,7 +106,7 @@ def rmsnorm_bwd(dy, h, weight, rstd, dh_in=None):
     dx = torch.empty_like(h2)
     dw = torch.empty_like(w) if w is not None else None
     L = _lib.lib()
-    with torch.cuda.device(dev):
+    with _on(dev):
         nbytes = L.b200k_rmsnorm_bwd_scratch_bytes(rows, hidden) if w is not None else 0
         scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev) if w is not None else None
         rc = L.b200k_rmsnorm_bwd(
@@ -109,7 +126,7 @@ def swiglu_fwd(a, b):
     dev = _require_cuda(a, b)
     a, b = _contig(a), _contig(b)
     out = torch.empty_like(a)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_swiglu_fwd(_ptr(a), _ptr(b), _ptr(out), a.numel(), _code(a), _stream(dev))
     _lib.check(rc, "b200k_swiglu_fwd")
     return out
@@ -120,7 +137,7 @@ def swiglu_bwd(a, b, g):
     dev = _require_cuda(a, b, g)
     a, b, g = _contig(a), _contig(b), _contig(g)
     da, db = torch.empty_like(a), torch.empty_like(a)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_swiglu_bwd(_ptr(a), _ptr(b), _ptr(g), _ptr(da), _ptr(db), a.numel(), _code(a), _stream(dev))
     _lib.check(rc, "b200k_swiglu_bwd")
     return da, db
@@ -140,7 +157,7 @@ def cross_entropy_fwd(logits, target, ignore_index: int = -100, reduction: str =
     row_max, row_logsum, row_nll = torch.empty(rows, **f32), torch.empty(rows, **f32), torch.empty(rows, **f32)
     loss = torch.empty((), dtype=logits.dtype, device=dev)
     n_valid = torch.empty((), dtype=torch.int64, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_cross_entropy_fwd(
             _ptr(logits), _ptr(target), _ptr(row_max), _ptr(row_logsum), _ptr(row_nll), _ptr(loss), _ptr(n_valid),
             rows, vocab, int(ignore_index), REDUCTION_CODE[reduction], _code(logits), _stream(dev),
@@ -156,7 +173,7 @@ def cross_entropy_bwd(g, logits, target, row_max, row_logsum, n_valid, ignore_in
     rows, vocab = logits.shape
     g = g.to(logits.dtype) if g.dtype != logits.dtype else g
     dlogits = torch.empty_like(logits)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_cross_entropy_bwd(
             _ptr(g), _ptr(logits), _ptr(target), _ptr(row_max), _ptr(row_logsum), _ptr(n_valid), _ptr(dlogits),
             rows, vocab, int(ignore_index), REDUCTION_CODE[reduction], _code(logits), _stream(dev),
@@ -180,7 +197,7 @@ def qkv_rope_fwd(qkv, cos, sin, n_head: int, n_query_groups: int, head_size: int
     q = torch.empty(B, n_head, T, head_size, dtype=qkv.dtype, device=dev)
     k = torch.empty(B, hkv, T, head_size, dtype=qkv.dtype, device=dev)
     v = torch.empty(B, hkv, T, head_size, dtype=qkv.dtype, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_qkv_rope_fwd(
             _ptr(qkv), _ptr(cos), _ptr(sin), _ptr(q), _ptr(k), _ptr(v), B, T, n_query_groups, qpk, head_size, rope_n_elem,
             int(expand), _code(qkv), _stream(dev),
@@ -197,7 +214,7 @@ def qkv_rope_bwd(dq, dk, dv, cos, sin, n_head: int, n_query_groups: int, head_si
     qpk = n_head // n_query_groups
     expand = _expand_kv(n_head, n_query_groups)
     dqkv = torch.empty(B, T, (n_head + 2 * n_query_groups) * head_size, dtype=dq.dtype, device=dev)
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_qkv_rope_bwd(
             _ptr(dq), _ptr(dk), _ptr(dv), _ptr(cos), _ptr(sin), _ptr(dqkv), B, T, n_query_groups, qpk, head_size, rope_n_elem,
             int(expand), _code(dq), _stream(dev),
@@ -218,7 +235,7 @@ def bias_act_fwd(x, bias, act: str, return_pre: bool = False):
     out = torch.empty_like(x2)
     pre = torch.empty_like(x2) if return_pre else None
     rows, hidden = x2.shape
-    with torch.cuda.device(dev):
+    with _on(dev):
         rc = _lib.lib().b200k_bias_act_fwd(_ptr(x2), _ptr(b), _ptr(out), _ptr(pre), rows, hidden, ACT_CODE[act], _code(x), _stream(dev))
     _lib.check(rc, "b200k_bias_act_fwd")
     return (out.view(shape), pre.view(shape)) if return_pre else out.view(shape)
@@ -236,7 +253,7 @@ def bias_act_bwd(x, bias, g, act: str, want_dbias: bool | None = None):
     dx = torch.empty_like(x2)
     db = torch.empty(hidden, dtype=x.dtype, device=dev) if want else None
     L = _lib.lib()
-    with torch.cuda.device(dev):
+    with _on(dev):
         nbytes = L.b200k_bias_act_bwd_scratch_bytes(rows, hidden) if want else 0
         scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev) if want else None
         rc = L.b200k_bias_act_bwd(
@@ -253,7 +270,7 @@ def colsum(x):
     rows, hidden = x2.shape
     out = torch.empty(hidden, dtype=x.dtype, device=dev)
     L = _lib.lib()
-    with torch.cuda.device(dev):
+    with _on(dev):
         nbytes = L.b200k_bias_act_bwd_scratch_bytes(rows, hidden)
         scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
         rc = L.b200k_colsum(_ptr(x2), _ptr(out), _ptr(scratch), nbytes, rows, hidden, _code(x), _stream(dev))

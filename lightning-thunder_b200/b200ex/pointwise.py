@@ -25,6 +25,7 @@ from dataclasses import dataclass
 import torch
 
 from . import _lib
+from .ops import _on
 
 MAX_IN, MAX_OUT, MAX_REG, MAX_CODE = 10, 6, 48, 192
 
@@ -428,7 +429,7 @@ class PwLaunch:
                 P.inp[k].ptr = t.data_ptr()
             for k, (name, _, _) in enumerate(spec.outputs):
                 P.out[k].ptr = outs[name].data_ptr()
-            with torch.cuda.device(dev):
+            with _on(dev):
                 rc = _lib.lib().b200k_pointwise(ctypes.byref(P), torch.cuda.current_stream(dev).cuda_stream)
         _lib.check(rc, "b200k_pointwise")
         return outs
