@@ -135,6 +135,10 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
             "b200_launches_per_step": region_census(thunder, jm) if args.executor == "b200" else {},
             "clocks": clocks,
         }
+        if args.executor == "b200":
+            from b200ex import jit
+
+            line["pointwise_jit"] = dict(jit.cache_info(), enabled=jit.enabled())  # generic pointwise regions: NVRTC-specialised kernels
         line["gpu_launches"] = sum(line["b200_launches_per_step"].values()) * args.steps
         if emit:
             print(json.dumps(line), flush=True)

