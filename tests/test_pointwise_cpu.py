@@ -106,3 +106,23 @@ def test_register_resident_encoding():
     outs = ["z"] + [f"m{i}" for i in range(1, 6)]
     (spec,) = compile_region({"x": (F32, (4,))}, nodes2, outs)
     assert spec.small_code is None and spec.code
+
+
+def test_jit_source_generation_and_nvrtc_compile():
+    """The run-time specialised path: straight-line CUDA C for a program, compiled by NVRTC for sm_100a (no GPU needed)."""
+    from b200ex import jit
+
+    nodes = [PwNode("broadcast_in_dim", "bb", BF, (4, 64), ("b", (1,))), PwNode("convert", "xf", F32, (4, 64), ("x",)),
+             PwNode("convert", "bf", F32, (4, 64), ("bb",)), PwNode("add", "a", F32, (4, 64), ("xf", "bf")),
+             PwNode("gt", "m", torch.bool, (4, 64), ("a", 0.0)), PwNode("where", "w", F32, (4, 64), ("m", "a", 0.0)),
+             PwNode("convert", "o", BF, (4, 64), ("w",))]
+    (spec,) = compile_region({"x": (BF, (4, 64)), "b": (BF, (64,))}, nodes, ["o", "m"])
+    assert spec.ssa and spec.out_ids and spec.leaf_dtypes == [BF, BF]
+    src = jit.generate_source(spec, (True, False), False, jit.unroll_for(2))
+    assert "pw_kernel" in src and "__fadd_rn" in src and "st_bool" in src and src.count("ld_bf16(P.in[0]") == jit.unroll_for(2)
+    if not jit.enabled():
+        pytest.skip("cuda-python / NVRTC not importable here")
+    cubin = jit.compile_cubin(src)
+    assert cubin[:4] == b"\x7fELF"
+    with pytest.raises(jit.JitUnavailable):
+        jit.compile_cubin("this is not CUDA")
