@@ -171,8 +171,17 @@ def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
     leaf_ids: dict = {}
     consts: dict = {}
 
+    cse: dict = {}
+
     def emit(op, a=-1, b=-1, c=-1, imm=None):
-        ssa.append((op, a, b, c, imm))
+        # common-subexpression elimination inside the region (the reference does it with nvFuserExecutor.cse,
+        # nvfuserex_impl.py:743-833): the same op on the same values is computed once
+        key = (op, a, b, c, imm)
+        if op != "leaf" and key in cse:
+            return cse[key]
+        ssa.append(key)
+        if op != "leaf":
+            cse[key] = len(ssa) - 1
         return len(ssa) - 1
 
     def const(x):

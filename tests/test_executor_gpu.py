@@ -213,3 +213,67 @@ def test_llama3_8b_block_full_size():
     assert rel(res["b200"][1], res["torch"][1]) < 2e-2
     for n, g in res["b200"][2].items():
         assert rel(g, res["torch"][2][n]) < 2e-2, f"grad {n}"
+
+
+class _Gpt2Block(torch.nn.Module):
+    def __init__(self, d, heads):
+        super().__init__()
+        self.ln1, self.ln2 = torch.nn.LayerNorm(d), torch.nn.LayerNorm(d)
+        self.attn, self.proj = torch.nn.Linear(d, 3 * d), torch.nn.Linear(d, d)
+        self.fc, self.out = torch.nn.Linear(d, 4 * d), torch.nn.Linear(4 * d, d)
+        self.heads = heads
+
+    def forward(self, x):
+        B, T, C = x.shape
+        q, k, v = self.attn(self.ln1(x)).split(C, dim=2)
+        q, k, v = (t.view(B, T, self.heads, C // self.heads).transpose(1, 2) for t in (q, k, v))
+        att = (q @ k.transpose(-2, -1)) * (1.0 / (C // self.heads) ** 0.5)
+        att = att.masked_fill(torch.ones(T, T, device=x.device, dtype=torch.bool).tril().logical_not(), float("-inf"))
+        y = (F.softmax(att, dim=-1) @ v).transpose(1, 2).contiguous().view(B, T, C)
+        x = x + self.proj(y)
+        return x + self.out(F.gelu(self.fc(self.ln2(x))))
+
+
+class _Gpt2(torch.nn.Module):
+    def __init__(self, vocab=256, block=64, d=128, heads=4, layers=2):
+        super().__init__()
+        self.wte, self.wpe = torch.nn.Embedding(vocab, d), torch.nn.Embedding(block, d)
+        self.h = torch.nn.ModuleList(_Gpt2Block(d, heads) for _ in range(layers))
+        self.ln_f = torch.nn.LayerNorm(d)
+        self.head = torch.nn.Linear(d, vocab, bias=False)
+
+    def forward(self, idx, targets):
+        pos = torch.arange(0, idx.shape[1], device=idx.device)
+        x = self.wte(idx) + self.wpe(pos)
+        for b in self.h:
+            x = b(x)
+        logits = self.head(self.ln_f(x))
+        return F.cross_entropy(logits.view(-1, logits.size(-1)), targets.view(-1), ignore_index=-1)
+
+
+def test_tiny_gpt2_forward_backward():
+    """A second model family (nanoGPT-style: LayerNorm, biased linears, GELU, learned positions, explicit masked softmax
+    attention): everything b200 does not claim stays with the torch executor, regions in between are ours, and loss and
+    parameter gradients agree with the all-torch run."""
+    torch.manual_seed(0)
+    model = _Gpt2().to(DEV).to(BF)
+    idx = torch.randint(0, 256, (2, 64), device=DEV)
+    tgt = torch.randint(0, 256, (2, 64), device=DEV)
+    tgt[1, :7] = -1
+    results = {}
+    for name, execs in (("b200", [b200.ex]), ("torch", ["torch"])):
+        model.zero_grad(set_to_none=True)
+        jm = thunder.jit(model, executors=execs)
+        loss = jm(idx, tgt)
+        loss.backward()
+        results[name] = (loss.detach().clone(), {n: p.grad.detach().clone() for n, p in model.named_parameters()}, jm)
+    torch.cuda.synchronize()
+    jm = results["b200"][2]
+    fk = [k for _, ks in fusions(thunder.last_traces(jm)[-1]) for k in ks]
+    bk = [k for _, ks in fusions(thunder.last_backward_traces(jm)[-1]) for k in ks]
+    assert "b200_cross_entropy_fwd" in fk and "b200_cross_entropy_bwd" in bk and len(fk) > 4 and len(bk) > 4
+    torch.testing.assert_close(results["b200"][0].float(), results["torch"][0].float(), rtol=1.6e-2, atol=1e-5)
+    for n, g in results["b200"][1].items():
+        ref = results["torch"][1][n]
+        err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
+        assert err.item() < 2e-2, f"grad {n}: relative error {err.item():.3e}"
