@@ -211,6 +211,39 @@ B200K_API int b200k_colsum(const void* x, void* out, void* scratch, int64_t scra
                            int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * LayerNorm over the last dimension, forward — SURVEY §8 row f.1.
+ * Replaces the region the reference builds from ltorch.layer_norm -> _native_layer_norm -> _normalize
+ * (thunder/torch/__init__.py:4406-4447): var_mean, rsqrt, scale, shift.
+ *   mean = sum_j f32(x) / hidden,  var = sum_j (f32(x) - mean)^2 / hidden     fp32 [rows]
+ *   rstd = rsqrt(var + eps)                                                    fp32 [rows]
+ *   y    = round_T((((f32(x) - mean) * rstd) * f32(weight)) + f32(bias))       (NULL weight / bias: step skipped)
+ * x, y: [rows, hidden] row-major contiguous of `dtype`; weight, bias: [hidden] of `dtype`.
+ * mean_out / rstd_out may be NULL.
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_layernorm_fwd(const void* x, const void* weight, const void* bias, void* y, float* mean_out,
+                        float* rstd_out, int64_t rows, int64_t hidden, float eps, int dtype, void* stream);
+
+/* Size in bytes of the scratch buffer b200k_layernorm_bwd needs for (rows, hidden). */
+B200K_API int64_t b200k_layernorm_bwd_scratch_bytes(int64_t rows, int64_t hidden);
+
+/* ---------------------------------------------------------------------------------------------
+ * LayerNorm backward — SURVEY §8 row f.1.  The program autodiff derives from the forward above: the
+ * mul / add / sub / rsqrt vjps plus the var_mean rule (thunder/core/transforms.py:1292-1312).
+ *   g      = f32(dy),  gw = f32(weight) * g,  xc = f32(x) - mean
+ *   direct = rstd * gw
+ *   c1     = sum_j xc * gw,  c2 = sum_j -direct
+ *   stats  = (1/hidden) * c2 + ((2 * ((-0.5 * c1) * rstd^3)) * xc) / hidden
+ *   dx     = round_T(round_T(direct) + round_T(stats))      (fp32: direct + stats)
+ *   dw     = round_T(sum_rows round_T((xc * rstd) * g)),  db = round_T(sum_rows g)
+ * weight NULL <-> dw NULL; db is written iff non-NULL.  mean, rstd: fp32 [rows] from the forward.
+ * scratch: device buffer of at least b200k_layernorm_bwd_scratch_bytes(rows, hidden) bytes, 16-byte aligned
+ * (contents ignored on entry, unspecified on exit); may be NULL when dw and db are both NULL.
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_layernorm_bwd(const void* dy, const void* x, const void* weight, const float* mean, const float* rstd,
+                        void* dx, void* dw, void* db, void* scratch, int64_t scratch_bytes, int64_t rows,
+                        int64_t hidden, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Generic pointwise region — SURVEY §8 rows a3/a4.  Executes a fused region made only of elementwise
  * prims, convert_element_type and broadcast_in_dim (the claimable vocabulary of
  * thunder/executors/nvfuserex_impl.py:971-2514 restricted to pointwise work) as ONE pass over memory:

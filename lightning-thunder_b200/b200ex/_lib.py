@@ -44,11 +44,14 @@ EXPORTS: dict[str, tuple] = {
     "b200k_bias_act_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int64, c_int, c_int, c_void_p]),
     "b200k_bias_act_bwd_scratch_bytes": (c_int64, [c_int64, c_int64]),
     "b200k_bias_act_bwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_int64, c_int, c_int, c_void_p]),
+    "b200k_layernorm_fwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_float, c_int, c_void_p]),
+    "b200k_layernorm_bwd_scratch_bytes": (c_int64, [c_int64, c_int64]),
+    "b200k_layernorm_bwd": (c_int, [c_void_p] * 9 + [c_int64, c_int64, c_int64, c_int, c_void_p]),
     "b200k_colsum": (c_int, [c_void_p] * 3 + [c_int64, c_int64, c_int64, c_int, c_void_p]),
     "b200k_pointwise": (c_int, [c_void_p, c_void_p]),
 }
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 _lock = threading.Lock()
 _lib = None

@@ -362,6 +362,66 @@ ex.register_supported(b200_rms_norm_bwd.id)
 ex.register_supported(ltorch.rms_norm, _rms_norm_check, execution_transform=_rms_norm_transform, grad_transform=_rms_norm_grad)
 
 
+# ---- LayerNorm (the normalisation of GPT-2 / BERT style blocks) ---------------------------
+def _layer_norm_fwd_meta(a, weight, bias, eps):
+    stat = tuple(a.shape[:-1]) + (1,)
+    return TensorProxy(like=a), TensorProxy(like=a, shape=stat, dtype=dtypes.float32), TensorProxy(like=a, shape=stat, dtype=dtypes.float32)
+
+
+def _layer_norm_fwd_impl(a, weight, bias, eps):
+    return ops.layernorm_fwd(a, weight, bias, eps)
+
+
+def _layer_norm_bwd_meta(dy, a, weight, mean, rstd, has_bias):
+    da = TensorProxy(like=a)
+    dw = TensorProxy(like=weight) if weight is not None else None
+    db = TensorProxy(like=a, shape=(a.shape[-1],)) if has_bias else None
+    return da, dw, db
+
+
+def _layer_norm_bwd_impl(dy, a, weight, mean, rstd, has_bias):
+    return ops.layernorm_bwd(dy, a, weight, mean, rstd, bool(has_bias))
+
+
+b200_layer_norm_fwd = ex.register_operator("b200_layer_norm_fwd", meta=_layer_norm_fwd_meta, fn=_layer_norm_fwd_impl, tags=[prims.OpTags.REDUCTION_OP])
+b200_layer_norm_bwd = ex.register_operator("b200_layer_norm_bwd", meta=_layer_norm_bwd_meta, fn=_layer_norm_bwd_impl, tags=[prims.OpTags.REDUCTION_OP])
+
+
+def _layer_norm_check(a, /, normalized_shape, weight=None, bias=None, eps=1e-5) -> bool:
+    # One normalised dimension (the last); weight / bias of the input's dtype.  The reference takes the shape from
+    # weight / bias when given (thunder/torch/__init__.py:4440-4446), so only their rank is looked at here.
+    if not _is_cuda_float(a) or a.ndim < 1 or not isinstance(eps, (int, float)):
+        return False
+    for p in (weight, bias):
+        if p is not None and (not _is_cuda_float(p) or p.dtype != a.dtype or tuple(p.shape) != (a.shape[-1],)):
+            return False
+    if weight is None and bias is None:
+        return len(normalized_shape) == 1 and normalized_shape[0] == a.shape[-1]
+    return True
+
+
+def _layer_norm_transform(a, /, normalized_shape, weight=None, bias=None, eps=1e-5):
+    y, _, _ = b200_layer_norm_fwd(a, weight, bias, float(eps))
+    return y
+
+
+def _layer_norm_grad(a, /, normalized_shape, weight=None, bias=None, eps=1e-5):
+    y, mean, rstd = b200_layer_norm_fwd(a, weight, bias, float(eps))
+    g = get_grad(y)
+    da, dw, db = b200_layer_norm_bwd(g, a, weight, mean, rstd, bias is not None)
+    put_grads((a,), (da,))
+    if weight is not None:
+        put_grads((weight,), (dw,))
+    if bias is not None:
+        put_grads((bias,), (db,))
+    return y
+
+
+ex.register_supported(b200_layer_norm_fwd.id)
+ex.register_supported(b200_layer_norm_bwd.id)
+ex.register_supported(ltorch.layer_norm, _layer_norm_check, execution_transform=_layer_norm_transform, grad_transform=_layer_norm_grad)
+
+
 # ---- cross-entropy ---------------------------------------------------------------------------------
 def _ce_fwd_meta(a, target, ignore_index, reduction):
     loss = TensorProxy(like=a, shape=())
@@ -550,6 +610,8 @@ ex.register_supported(b200_swiglu_bwd.id)
 _MACRO_IMPL: dict[Any, Callable] = {
     b200_rms_norm_fwd.id: _rms_norm_fwd_impl,
     b200_rms_norm_bwd.id: _rms_norm_bwd_impl,
+    b200_layer_norm_fwd.id: _layer_norm_fwd_impl,
+    b200_layer_norm_bwd.id: _layer_norm_bwd_impl,
     b200_cross_entropy_fwd.id: _ce_fwd_impl,
     b200_cross_entropy_bwd.id: _ce_bwd_impl,
     b200_qkv_split_rope.id: _rope_fwd_impl,

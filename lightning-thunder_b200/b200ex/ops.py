@@ -15,7 +15,8 @@ from . import _lib
 
 __all__ = [
     "rmsnorm_fwd", "rmsnorm_bwd", "swiglu_fwd", "swiglu_bwd", "cross_entropy_fwd", "cross_entropy_bwd",
-    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "colsum", "ACT_CODE", "DTYPE_CODE",
+    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "colsum", "layernorm_fwd", "layernorm_bwd",
+    "ACT_CODE", "DTYPE_CODE",
 ]
 
 DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
@@ -65,6 +66,10 @@ def _ptr(t):
 
 def _stream(dev: torch.device) -> int:
     return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _contig(t):
+    return t if t.is_contiguous() else t.contiguous()
 
 
 def _rows2d(t: torch.Tensor) -> torch.Tensor:
@@ -117,8 +122,48 @@ def rmsnorm_bwd(dy, h, weight, rstd, dh_in=None):
     return dx.view(shape), dw
 
 
-def _contig(t):
-    return t if t.is_contiguous() else t.contiguous()
+def layernorm_fwd(x, weight, bias, eps: float):
+    """(y, mean, rstd) = LayerNorm over the last dimension — see b200k_layernorm_fwd.
+    mean and rstd have shape x.shape[:-1] + (1,) in fp32."""
+    dev = _require_cuda(x, weight, bias)
+    xc = _contig(x)
+    w = _contig(weight) if weight is not None else None
+    b = _contig(bias) if bias is not None else None
+    hidden = xc.shape[-1]
+    rows = xc.numel() // hidden if hidden else 0
+    y = torch.empty_like(xc)
+    stat_shape = tuple(xc.shape[:-1]) + (1,)
+    mean = torch.empty(stat_shape, dtype=torch.float32, device=dev)
+    rstd = torch.empty(stat_shape, dtype=torch.float32, device=dev)
+    with _on(dev):
+        rc = _lib.lib().b200k_layernorm_fwd(
+            xc.data_ptr(), _ptr(w), _ptr(b), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), rows, hidden, float(eps), _code(x), _stream(dev)
+        )
+    _lib.check(rc, "b200k_layernorm_fwd")
+    return y, mean, rstd
+
+
+def layernorm_bwd(dy, x, weight, mean, rstd, want_dbias: bool):
+    """(dx, dw, db) — see b200k_layernorm_bwd.  dw is None when weight is None, db is None unless want_dbias."""
+    dev = _require_cuda(dy, x, weight, mean, rstd)
+    dyc, xc, mu, rs = _contig(dy), _contig(x), _contig(mean), _contig(rstd)
+    w = _contig(weight) if weight is not None else None
+    hidden = xc.shape[-1]
+    rows = xc.numel() // hidden if hidden else 0
+    dx = torch.empty_like(xc)
+    dw = torch.empty_like(w) if w is not None else None
+    db = torch.empty(hidden, dtype=x.dtype, device=dev) if want_dbias else None
+    L = _lib.lib()
+    with _on(dev):
+        need = w is not None or want_dbias
+        nbytes = L.b200k_layernorm_bwd_scratch_bytes(rows, hidden) if need else 0
+        scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev) if need else None
+        rc = L.b200k_layernorm_bwd(
+            dyc.data_ptr(), xc.data_ptr(), _ptr(w), mu.data_ptr(), rs.data_ptr(), dx.data_ptr(), _ptr(dw), _ptr(db), _ptr(scratch), nbytes,
+            rows, hidden, _code(x), _stream(dev),
+        )
+    _lib.check(rc, "b200k_layernorm_bwd")
+    return dx, dw, db
 
 
 def swiglu_fwd(a, b):

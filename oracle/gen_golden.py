@@ -176,6 +176,31 @@ def case_ce(gen, dtype, rows, vocab, ignore_index, n_ignored):
     }
 
 
+def case_layernorm(gen, dtype, rows, hidden, eps=1e-5, bias=True):
+    x = _rand(gen, (rows, hidden), dtype, 1.5) + 0.25
+    w, b = _rand(gen, (hidden,), dtype), _rand(gen, (hidden,), dtype)
+    dy = _rand(gen, (rows, hidden), dtype)
+
+    if bias:
+        def fn(x, w, b):
+            return F.layer_norm(x, (hidden,), w, b, eps)
+        ins, names = {"x": x, "w": w, "b": b}, ["x", "w", "b"]
+    else:
+        def fn(x, w):
+            return F.layer_norm(x, (hidden,), w, None, eps)
+        ins, names = {"x": x, "w": w}, ["x", "w"]
+
+    (y,), g = _run_ref(fn, ins, names, [dy])
+    oy, mean, rstd = O.layernorm_fwd(x, w, b if bias else None, eps)
+    odx, odw, odb = O.layernorm_bwd(dy, x, w, bias, mean, rstd)
+    _same(oy, y, "layernorm y"), _same(odx, g["x"], "layernorm dx"), _same(odw, g["w"], "layernorm dw")
+    outs = {"y": y, "dx": g["x"], "dw": g["w"]}
+    if bias:
+        _same(odb, g["b"], "layernorm db")
+        outs["db"] = g["b"]
+    return {"inputs": {**ins, "dy": dy}, "outputs": outs, "meta": {"eps": eps, "bias": bias}}
+
+
 def main():
     gen = torch.Generator().manual_seed(20261106)
     cases = {}
@@ -199,6 +224,11 @@ def main():
     cases["ce_bf16_8x4096_ignm1"] = case_ce(gen, torch.bfloat16, 8, 4096, -1, 2)
     cases["ce_f32_16x300"] = case_ce(gen, torch.float32, 16, 300, -100, 0)
     cases["ce_f16_8x129"] = case_ce(gen, torch.float16, 8, 129, -100, 1)
+    for name, dt in DT.items():
+        cases[f"layernorm_{name}_16x256"] = case_layernorm(gen, dt, 16, 256)
+    cases["layernorm_bf16_5x768"] = case_layernorm(gen, torch.bfloat16, 5, 768)
+    cases["layernorm_bf16_7x100_nobias"] = case_layernorm(gen, torch.bfloat16, 7, 100, bias=False)  # unaligned hidden
+    cases["layernorm_f32_3x1000"] = case_layernorm(gen, torch.float32, 3, 1000, eps=1e-6)
 
     out = os.path.join(ROOT, "tests", "golden", "regions.pt")
     os.makedirs(os.path.dirname(out), exist_ok=True)

@@ -35,6 +35,8 @@ __all__ = [
     "bias_relu_bwd",
     "cross_entropy_fwd",
     "cross_entropy_bwd",
+    "layernorm_fwd",
+    "layernorm_bwd",
 ]
 
 
@@ -334,3 +336,63 @@ def cross_entropy_bwd(g, logp, target, n_valid, ignore_index: int = -100):
         g, logp, target, None, 1, ignore_index, n_valid.to(logp.dtype) if n_valid.dtype != logp.dtype else n_valid
     )
     return torch.ops.aten._log_softmax_backward_data(dlogp, logp, 1, logp.dtype)
+
+
+# ----------------------------------------------------------------------------------------------
+# LayerNorm — SURVEY §8 row f.1 (the normalisation of the GPT-2 / BERT style blocks)
+# ----------------------------------------------------------------------------------------------
+def layernorm_fwd(x, weight, bias, eps: float):
+    """``F.layer_norm(x, (H,), weight, bias, eps)`` over the last dimension.
+
+    Follows ltorch.layer_norm -> _native_layer_norm -> _normalize (thunder/torch/__init__.py:4406-4447):
+    upcast, ``var_mean(correction=0)``, ``rsqrt(var + eps)``, ``(x - mean) * rstd``, times the upcast weight,
+    plus the upcast bias, downcast.  Returns (y, mean[rows,1] fp32, rstd[rows,1] fp32); weight / bias may be None.
+    """
+    dt = x.dtype
+    xf = _f32(x)
+    var, mean = torch.var_mean(xf, (-1,), correction=0)
+    var, mean = var.unsqueeze(-1), mean.unsqueeze(-1)
+    rstd = torch.rsqrt(torch.add(var, eps))
+    xc = torch.sub(xf, mean.expand(xf.shape))
+    out = torch.mul(xc, rstd.expand(xf.shape))
+    if weight is not None:
+        out = torch.mul(out, _f32(weight.expand(x.shape)))
+    if bias is not None:
+        out = torch.add(out, _f32(bias.expand(x.shape)))
+    return out.to(dt), mean, rstd
+
+
+def layernorm_bwd(dy, x, weight, has_bias: bool, mean, rstd):
+    """Backward of :func:`layernorm_fwd` as autodiff derives it: the mul/add/sub/rsqrt vjps plus the
+    var_mean rule (thunder/core/transforms.py:1292-1312: ``mean_grad = (1/H) * gm`` and
+    ``var_grad = (2 * gv * (x - mean)) / H``, summed first, then added to the direct term).
+
+    16-bit storage: the direct term ``rstd * (w * dy)`` and the statistics term are each rounded to the
+    storage dtype where the trace holds them as tensors, then added in that dtype.  dw sums the ROUNDED
+    products ``round(xhat * dy)``, db sums dy (both with fp32 accumulation inside ``torch.sum``).
+    Returns (dx, dw, db); dw / db are None when the parameter is absent.
+    """
+    dt = x.dtype
+    H = x.shape[-1]
+    lead = tuple(range(x.dim() - 1))
+    xf = _f32(x)
+    g = _f32(dy)
+    mean_b, rstd_b = mean.expand(xf.shape), rstd.expand(xf.shape)
+    xc = torch.sub(xf, mean_b)
+    xhat = torch.mul(xc, rstd_b)
+    db = torch.sum(g.to(dt), lead, False, dtype=None) if has_bias else None
+    if weight is not None:
+        gw = torch.mul(_f32(weight.expand(x.shape)), g)
+        dw = torch.sum(torch.mul(xhat, g).to(dt), lead, False, dtype=None)
+    else:
+        gw, dw = g, None
+    direct = torch.mul(rstd_b, gw)
+    c1 = torch.sum(torch.mul(xc, gw), (-1,), False).unsqueeze(-1)
+    c2 = torch.sum(torch.neg(direct), (-1,), False).unsqueeze(-1)
+    gvar = torch.mul(torch.mul(-0.5, c1), torch.pow(rstd, 3.0))
+    mean_grad = torch.mul(1.0 / H, c2.expand(xf.shape))
+    var_grad = torch.true_divide(torch.mul(torch.mul(2, gvar.expand(xf.shape)), torch.sub(xf, mean_b)), H)
+    stats = torch.add(mean_grad, var_grad)
+    if dt == torch.float32:
+        return torch.add(direct, stats), dw, db
+    return torch.add(direct.to(dt), stats.to(dt)), dw, db

@@ -65,6 +65,21 @@ def test_rmsnorm_residual(dtype):
     _compare(res, f"rmsnorm {dtype}", ulp=(lambda b: b.float().abs() + 4.0) if dtype is BF else None, grad_atol=0 if dtype is BF else 2e-5)
 
 
+@pytest.mark.parametrize("dtype", [BF, F32])
+@pytest.mark.parametrize("bias", [True, False])
+def test_layer_norm(dtype, bias):
+    def f(x, r, w, b):
+        h = x + r
+        return F.layer_norm(h, (768,), w, b if bias else None, 1e-5) * 2.0
+
+    args = [_mk(48, 768, dtype=dtype, seed=1), _mk(48, 768, dtype=dtype, seed=2), _mk(768, dtype=dtype, seed=3), _mk(768, dtype=dtype, seed=4, grad=bias)]
+    res = _both(f, args)
+    jf = res[0][2]
+    assert "b200_layer_norm_fwd" in [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks]
+    assert "b200_layer_norm_bwd" in [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks]
+    _compare(res, f"layer_norm {dtype}", ulp=lambda b: b.float().abs() * (1.0 if dtype is BF else 16.0) + 8.0, grad_atol=0 if dtype is BF else 2e-5)
+
+
 def test_swiglu_inline_expression():
     res = _both(lambda a, b: F.silu(a) * b, [_mk(128, 1024, seed=4, scale=2.0), _mk(128, 1024, seed=5)])
     kinds = [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
@@ -253,8 +268,8 @@ class _Gpt2(torch.nn.Module):
 
 def test_tiny_gpt2_forward_backward():
     """A second model family (nanoGPT-style: LayerNorm, biased linears, GELU, learned positions, explicit masked softmax
-    attention): everything b200 does not claim stays with the torch executor, regions in between are ours, and loss and
-    parameter gradients agree with the all-torch run."""
+    attention): LayerNorm, bias + GELU and cross-entropy run on our kernels, everything b200 does not claim stays with the
+    torch executor, and loss and parameter gradients agree with the all-torch run."""
     torch.manual_seed(0)
     model = _Gpt2().to(DEV).to(BF)
     idx = torch.randint(0, 256, (2, 64), device=DEV)
@@ -271,7 +286,8 @@ def test_tiny_gpt2_forward_backward():
     jm = results["b200"][2]
     fk = [k for _, ks in fusions(thunder.last_traces(jm)[-1]) for k in ks]
     bk = [k for _, ks in fusions(thunder.last_backward_traces(jm)[-1]) for k in ks]
-    assert "b200_cross_entropy_fwd" in fk and "b200_cross_entropy_bwd" in bk and len(fk) > 4 and len(bk) > 4
+    assert "b200_cross_entropy_fwd" in fk and "b200_cross_entropy_bwd" in bk
+    assert fk.count("b200_layer_norm_fwd") == 5 and bk.count("b200_layer_norm_bwd") == 5
     torch.testing.assert_close(results["b200"][0].float(), results["torch"][0].float(), rtol=1.6e-2, atol=1e-5)
     for n, g in results["b200"][1].items():
         ref = results["torch"][1][n]
