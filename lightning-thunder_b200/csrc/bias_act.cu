@@ -5,6 +5,7 @@
 // registers and the backward can keep fp32 partial column sums of dx per thread (dbias), written as
 // one partial row per CTA and folded by colsum_finalize (deterministic, no atomics).
 // act: 0 = none (bias add only), 1 = relu, 2 = gelu (erf form).
+#include <cstdlib>
 #include <type_traits>
 
 #include "common.cuh"
@@ -118,9 +119,68 @@ __device__ __forceinline__ void act_bwd(const float* a, const float* g, float* d
     }
 }
 
+// ---- bf16 storage, GELU: the chain on packed bf16x2 words --------------------------------------------------
+// Every ltorch op of the reference's trace takes bf16 tensors, computes in fp32 and rounds the result to bf16.
+// When both operands are bf16 VALUES (tensor x tensor, or tensor x a constant bf16 holds exactly, like 0.5) the
+// fp32 result is exact for a product (8 + 8 significand bits) and within fp32 for a sum wherever the small
+// operand can still move the result, so one rounding of the exact result — what HMUL2.BF16 / HADD2.BF16 do —
+// equals the reference's two-step rounding bit for bit.  Those ops then need no unpack / repack at all: one
+// instruction per pair instead of five.  Ops with an fp32-only constant (1/sqrt2) and the transcendental parts
+// stay in fp32.  The _rn intrinsics matter: plain __hmul2 + __hadd2 may be contracted into one HFMA2, which skips
+// the product's rounding.  The test-suite compares this path with the fp32 form bit for bit (B200K_BIAS_ACT_PACKED=0).
+__device__ __forceinline__ uint32_t bf2_add(uint32_t a, uint32_t b) {
+    const __nv_bfloat162 r = __hadd2_rn(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+    return *reinterpret_cast<const uint32_t*>(&r);
+}
+__device__ __forceinline__ uint32_t bf2_mul(uint32_t a, uint32_t b) {
+    const __nv_bfloat162 r = __hmul2_rn(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+    return *reinterpret_cast<const uint32_t*>(&r);
+}
+constexpr uint32_t kBf2Half = 0x3F003F00u;  // (0.5, 0.5)
+
+// erf(z) by Abramowitz-Stegun 7.1.26 as in erf2<true>; also hands back e = exp(-z^2), which the backward's
+// density term needs again.
+__device__ __forceinline__ float2 erf2_with_exp(float2 z, float2& e_out) {
+    const float2 ax = make_float2(fabsf(z.x), fabsf(z.y));
+    const float2 d = __ffma2_rn(f2(0.3275911f), ax, f2(1.0f));
+    const float2 t = make_float2(hw_rcp(d.x), hw_rcp(d.y));
+    const float2 q = __fmul2_rn(__fmul2_rn(ax, ax), f2(-1.4426950408889634f));
+    const float2 e = make_float2(hw_ex2(q.x), hw_ex2(q.y));
+    e_out = e;
+    float2 p = __ffma2_rn(f2(1.061405429f), t, f2(-1.453152027f));
+    p = __ffma2_rn(p, t, f2(1.421413741f));
+    p = __ffma2_rn(p, t, f2(-0.284496736f));
+    p = __ffma2_rn(p, t, f2(0.254829592f));
+    const float2 r = __ffma2_rn(__fmul2_rn(p, t), make_float2(-e.x, -e.y), f2(1.0f));
+    return make_float2(copysignf(r.x, z.x), copysignf(r.y, z.y));
+}
+
+// cdf word = 0.5 + 0.5 * erf(a / sqrt2), each step rounded; e_out = exp(-z^2) of the rounded z
+__device__ __forceinline__ uint32_t gelu_cdf_word(uint32_t a2, float2& e_out) {
+    using V = Vec<__nv_bfloat16>;
+    const float2 z = V::rnd2f(__fmul2_rn(V::word2(a2), f2(kInvSqrt2)));
+    const uint32_t erf_w = V::pack_word(erf2_with_exp(z, e_out));
+    return bf2_add(bf2_mul(erf_w, kBf2Half), kBf2Half);
+}
+__device__ __forceinline__ uint32_t gelu_fwd_word(uint32_t a2) {
+    float2 e;
+    return bf2_mul(a2, gelu_cdf_word(a2, e));
+}
+__device__ __forceinline__ uint32_t gelu_bwd_word(uint32_t a2, uint32_t g2) {
+    using V = Vec<__nv_bfloat16>;
+    float2 e;
+    const uint32_t cdf = gelu_cdf_word(a2, e);
+    const uint32_t p = bf2_mul(cdf, g2);                          // cdf * g
+    const uint32_t q = bf2_mul(bf2_mul(a2, g2), kBf2Half);        // 0.5 * (a * g)
+    const float2 dens = __fmul2_rn(f2(kTwoOverSqrtPi), e);        // 2/sqrt(pi) * exp(-z^2), an fp32 tensor in the trace
+    const uint32_t r = V::pack_word(__fmul2_rn(dens, V::word2(q)));
+    const uint32_t r2 = V::pack_word(__fmul2_rn(V::word2(r), f2(kInvSqrt2)));
+    return bf2_add(p, r2);
+}
+
 // kAccum: keep fp32 column sums of the (rounded) backward result for dbias; kStore: write `out`;
 // pre_out (forward, nullable): also write the rounded pre-activation a = x + bias, which is what autodiff saves.
-template <typename T, int kAct, bool kHasBias, bool kBwd, bool kAccum, bool kStore = true>
+template <typename T, int kAct, bool kHasBias, bool kBwd, bool kAccum, bool kStore = true, bool kPacked = false>
 __global__ void __launch_bounds__(kBaThreads)
 bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __restrict__ g, T* __restrict__ out,
                 T* __restrict__ pre_out, float* __restrict__ partial, int64_t rows, int nvec) {
@@ -155,7 +215,33 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
 #pragma unroll
         for (int i = 0; i < kBaVpl; ++i) {
             const int v = v0 + i * nthr;
-            if (v < nvec) {
+            if constexpr (kPacked) {
+                if (v < nvec) {
+                    const uint32_t xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w};
+                    const uint32_t gw[4] = {gv[i].x, gv[i].y, gv[i].z, gv[i].w};
+                    uint32_t aw[4], ow[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        // bias was unpacked exactly, so repacking it is exact too
+                        aw[k] = kHasBias ? bf2_add(xw[k], V::pack_word(make_float2(bf[i][2 * k], bf[i][2 * k + 1]))) : xw[k];
+                        if constexpr (kBwd) {
+                            ow[k] = gelu_bwd_word(aw[k], gw[k]);
+                            if constexpr (kAccum) {
+                                const float2 d = V::word2(ow[k]);
+                                acc[i][2 * k] += d.x;
+                                acc[i][2 * k + 1] += d.y;
+                            }
+                        } else {
+                            ow[k] = gelu_fwd_word(aw[k]);
+                        }
+                    }
+                    if constexpr (!kBwd) {
+                        if (pre_out != nullptr)
+                            st_stream(reinterpret_cast<uint4*>(pre_out) + row * nvec + v, make_uint4(aw[0], aw[1], aw[2], aw[3]));
+                    }
+                    if constexpr (kStore) st_stream(reinterpret_cast<uint4*>(out) + row * nvec + v, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+                }
+            } else if (v < nvec) {
                 float a[kE], o[kE];
                 V::unpack(xv[i], a);
                 if constexpr (kHasBias) {
@@ -241,6 +327,15 @@ bias_act_generic_kernel(const T* __restrict__ x, const T* __restrict__ bias, con
     if (kBwd && dbias != nullptr) V::store1(dbias, col, acc);
 }
 
+// B200K_BIAS_ACT_PACKED=0 selects the fp32 form of the bf16 GELU chain (bit-for-bit comparison in the tests).
+bool packed_bf16_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("B200K_BIAS_ACT_PACKED");
+        return !(e != nullptr && e[0] == '0');
+    }();
+    return on;
+}
+
 int row_parts(int64_t rows, int col_tiles) {
     int64_t parts = static_cast<int64_t>(sm_count()) * kBaRowParts / (col_tiles > 0 ? col_tiles : 1);
     if (parts < 1) parts = 1;
@@ -276,6 +371,9 @@ int run(const void* x, const void* bias, const void* g, void* out, void* pre_out
     };
     auto pick = [&](auto has_bias, auto acc) {
         constexpr bool kB = decltype(has_bias)::value, kA = decltype(acc)::value;
+        if constexpr (V::kDtype == B200K_BF16) {
+            if (act == 2 && packed_bf16_enabled()) return go(bias_act_kernel<T, 2, kB, kBwd, kA, true, true>);
+        }
         return act == 0 ? go(bias_act_kernel<T, 0, kB, kBwd, kA>) : act == 1 ? go(bias_act_kernel<T, 1, kB, kBwd, kA>) : go(bias_act_kernel<T, 2, kB, kBwd, kA>);
     };
     int rc;

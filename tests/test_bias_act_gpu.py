@@ -98,3 +98,47 @@ def test_nanogpt_mlp_shape():
     g = torch.Generator().manual_seed(0)
     mk = lambda *s: torch.randn(*s, generator=g).to(torch.bfloat16)
     _check(mk(8192, 3072), mk(3072), mk(8192, 3072), "gelu", "nanogpt mlp")
+
+
+_FP32_FORM = r"""
+import os, sys, torch
+os.environ["B200K_BIAS_ACT_PACKED"] = "0"
+sys.path[:0] = [sys.argv[1]]
+from b200ex import ops
+d = torch.load(sys.argv[2])
+x, b, g = (d[k].cuda() for k in ("x", "b", "g"))
+out, pre = ops.bias_act_fwd(x, b, "gelu", return_pre=True)
+dx, db = ops.bias_act_bwd(x, b, g, "gelu")
+torch.save({"out": out.cpu(), "pre": pre.cpu(), "dx": dx.cpu(), "db": db.cpu()}, sys.argv[3])
+"""
+
+
+def test_packed_bf16_gelu_equals_the_fp32_form_bit_for_bit(tmp_path):
+    """The bf16 GELU chain runs on packed bf16x2 multiplies / adds where both operands are bf16 values; that is
+    claimed to round exactly like fp32-op-then-round.  Run the fp32 form in a second process
+    (B200K_BIAS_ACT_PACKED=0 is read once per process) on inputs that cover every bf16 exponent the activation
+    sees, including subnormal products, and compare all outputs bitwise."""
+    import os
+    import subprocess
+    import sys
+
+    from b200ex import ops
+
+    g0 = torch.Generator().manual_seed(5)
+    rows, hidden = 512, 2048
+    mag = torch.exp2(torch.randint(-30, 8, (rows, hidden), generator=g0).float())
+    x = (torch.randn(rows, hidden, generator=g0) * mag).to(torch.bfloat16)
+    x[:64] = (torch.randn(64, hidden, generator=g0) * 3).to(torch.bfloat16)  # the interesting range of erf
+    b = (torch.randn(hidden, generator=g0) * 0.5).to(torch.bfloat16)
+    g = (torch.randn(rows, hidden, generator=g0) * torch.exp2(torch.randint(-20, 4, (rows, hidden), generator=g0).float())).to(torch.bfloat16)
+    src, dst = tmp_path / "in.pt", tmp_path / "out.pt"
+    torch.save({"x": x, "b": b, "g": g}, src)
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lightning-thunder_b200")
+    subprocess.run([sys.executable, "-c", _FP32_FORM, pkg, str(src), str(dst)], check=True, timeout=300)
+    ref = torch.load(dst)
+    out, pre = ops.bias_act_fwd(x.to(DEV), b.to(DEV), "gelu", return_pre=True)
+    dx, db = ops.bias_act_bwd(x.to(DEV), b.to(DEV), g.to(DEV), "gelu")
+    torch.cuda.synchronize()
+    for name, t in (("out", out), ("pre", pre), ("dx", dx), ("db", db)):
+        a, e = t.cpu().view(torch.int16), ref[name].view(torch.int16)
+        assert torch.equal(a, e), f"{name}: {(a != e).sum().item()} of {a.numel()} words differ between the packed and the fp32 form"
