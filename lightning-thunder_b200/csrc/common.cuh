@@ -173,6 +173,52 @@ struct Vec<__half> {
 };
 
 // ---------------------------------------------------------------------------------------------
+// Packed 2 x 16-bit arithmetic on the 32-bit words of a vector (HMUL2 / HADD2, .BF16 or .F16).
+// The reference's trace computes every 16-bit op as: upcast both operands to fp32, operate, round to the
+// storage type.  When both operands are storage-type VALUES the fp32 product is exact (8 + 8 or 11 + 11
+// significand bits) and the fp32 sum is exact wherever the smaller operand can still affect the rounded
+// result, so the single rounding of the packed instruction gives the same bits — with no unpack / repack.
+// The _rn intrinsics are required: plain __hmul2 + __hadd2 may be contracted into one HFMA2, which skips the
+// product's rounding.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+struct Pk;
+template <>
+struct Pk<__nv_bfloat16> {
+    using P = __nv_bfloat162;
+    __device__ static __forceinline__ P as(uint32_t w) { return *reinterpret_cast<const P*>(&w); }
+    __device__ static __forceinline__ uint32_t u(P v) { return *reinterpret_cast<const uint32_t*>(&v); }
+    __device__ static __forceinline__ uint32_t mul(uint32_t a, uint32_t b) { return u(__hmul2_rn(as(a), as(b))); }
+    __device__ static __forceinline__ uint32_t add(uint32_t a, uint32_t b) { return u(__hadd2_rn(as(a), as(b))); }
+    __device__ static __forceinline__ uint32_t sub(uint32_t a, uint32_t b) { return u(__hsub2_rn(as(a), as(b))); }
+};
+template <>
+struct Pk<__half> {
+    using P = __half2;
+    __device__ static __forceinline__ P as(uint32_t w) { return *reinterpret_cast<const P*>(&w); }
+    __device__ static __forceinline__ uint32_t u(P v) { return *reinterpret_cast<const uint32_t*>(&v); }
+    __device__ static __forceinline__ uint32_t mul(uint32_t a, uint32_t b) { return u(__hmul2_rn(as(a), as(b))); }
+    __device__ static __forceinline__ uint32_t add(uint32_t a, uint32_t b) { return u(__hadd2_rn(as(a), as(b))); }
+    __device__ static __forceinline__ uint32_t sub(uint32_t a, uint32_t b) { return u(__hsub2_rn(as(a), as(b))); }
+};
+template <>
+struct Pk<float> {  // never executed: fp32 vectors take the scalar paths
+    __device__ static __forceinline__ uint32_t mul(uint32_t a, uint32_t) { return a; }
+    __device__ static __forceinline__ uint32_t add(uint32_t a, uint32_t) { return a; }
+    __device__ static __forceinline__ uint32_t sub(uint32_t a, uint32_t) { return a; }
+};
+// r = op(a * b, c * d) word by word
+template <typename T, bool kSub>
+__device__ __forceinline__ uint4 pk_mul_mul_add(const uint4& a, const uint4& b, const uint4& c, const uint4& d) {
+    using K = Pk<T>;
+    auto one = [](uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+        const uint32_t x = K::mul(a, b), y = K::mul(c, d);
+        return kSub ? K::sub(x, y) : K::add(x, y);
+    };
+    return make_uint4(one(a.x, b.x, c.x, d.x), one(a.y, b.y, c.y, d.y), one(a.z, b.z, c.z, d.z), one(a.w, b.w, c.w, d.w));
+}
+
+// ---------------------------------------------------------------------------------------------
 // Reductions.
 // ---------------------------------------------------------------------------------------------
 struct SumOp {

@@ -10,6 +10,8 @@
 // written once; items past the rotary span copy one vector per slot.  Consecutive threads take consecutive p,
 // so each warp reads and writes 128-byte runs.  kW = elements per vector (8/4 for 16-byte access, 1
 // for the scalar fallback when sizes or pointers are not 16-byte friendly).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200k {
@@ -132,7 +134,10 @@ constexpr int kTokTile = 16;  // tokens handled by neighbouring threads in the b
 constexpr int kBwdChunk = 4;  // expanded copies gathered together in the backward
 constexpr int kMaxQpk = 6;  // slots whose loads are issued together; larger groups loop in chunks
 
-template <typename T, int kW>
+// kPk (16-bit storage, 16-byte vectors): the rotation runs on packed 2 x 16-bit words (Pk<T> in common.cuh) —
+// vectors are never unpacked to fp32, which takes the kernel from 18 to 6 ALU instructions per word and frees
+// the registers for more loads in flight; bit-identical to the fp32 form (B200K_ROPE_PACKED=0, compared in the tests).
+template <typename T, int kW, bool kPk>
 __global__ void __launch_bounds__(128)
 rope_fwd_kernel(const T* __restrict__ qkv, const T* __restrict__ cosp, const T* __restrict__ sinp, T* __restrict__ q,
                 T* __restrict__ k, T* __restrict__ v, RopeShape s, int64_t nitems) {
@@ -153,12 +158,18 @@ rope_fwd_kernel(const T* __restrict__ qkv, const T* __restrict__ cosp, const T* 
         const int e0 = paired ? p * kW : (s.rope_n + (p - half) * kW);
         const int e1 = e0 + half * kW;
         const T* grp = qkv + (bt * s.G + g) * (static_cast<int64_t>(slots) * s.hs);
-        float clo[kW], chi[kW], slo[kW], shi[kW];
+        float clo[kPk ? 1 : kW], chi[kPk ? 1 : kW], slo[kPk ? 1 : kW], shi[kPk ? 1 : kW];
+        uint4 pclo, pchi, pslo, pshi;
         if (paired) {
-            ldv<T, kW>(cosp, t * s.rope_n + e0, clo, false);
-            ldv<T, kW>(cosp, t * s.rope_n + e1, chi, false);
-            ldv<T, kW>(sinp, t * s.rope_n + e0, slo, false);
-            ldv<T, kW>(sinp, t * s.rope_n + e1, shi, false);
+            if constexpr (kPk) {
+                pclo = ld_keep(cosp + t * s.rope_n + e0), pchi = ld_keep(cosp + t * s.rope_n + e1);
+                pslo = ld_keep(sinp + t * s.rope_n + e0), pshi = ld_keep(sinp + t * s.rope_n + e1);
+            } else {
+                ldv<T, kW>(cosp, t * s.rope_n + e0, clo, false);
+                ldv<T, kW>(cosp, t * s.rope_n + e1, chi, false);
+                ldv<T, kW>(sinp, t * s.rope_n + e0, slo, false);
+                ldv<T, kW>(sinp, t * s.rope_n + e1, shi, false);
+            }
         }
         for (int s0 = 0; s0 < slots; s0 += kMaxQpk) {
             Raw<kW> rlo[kMaxQpk], rhi[kMaxQpk];
@@ -175,6 +186,29 @@ rope_fwd_kernel(const T* __restrict__ qkv, const T* __restrict__ cosp, const T* 
                 const int slot = s0 + j;
                 if (slot < slots) {
                     const bool is_q = slot < s.qpk, is_k = slot == s.qpk;
+                    if constexpr (kPk) {
+                        uint4 olo = rlo[j].v, ohi = rhi[j].v;
+                        if (paired && (is_q || is_k)) {
+                            // out_lo = rnd(rnd(lo * cos_lo) - rnd(hi * sin_lo)),  out_hi = rnd(rnd(hi * cos_hi) + rnd(lo * sin_hi))
+                            olo = pk_mul_mul_add<T, true>(rlo[j].v, pclo, rhi[j].v, pslo);
+                            ohi = pk_mul_mul_add<T, false>(rhi[j].v, pchi, rlo[j].v, pshi);
+                        }
+                        if (is_q) {
+                            T* dst = q + ((b * nq + g * s.qpk + slot) * s.T + t) * s.hs;
+                            st_stream(dst + e0, olo);
+                            if (paired) st_stream(dst + e1, ohi);
+                        } else {
+                            T* base = is_k ? k : v;
+                            const int reps = s.expand ? s.qpk : 1;
+                            for (int rr = 0; rr < reps; ++rr) {
+                                const int head = s.expand ? g * s.qpk + rr : g;
+                                T* dst = base + ((b * hkv + head) * s.T + t) * s.hs;
+                                st_stream(dst + e0, olo);
+                                if (paired) st_stream(dst + e1, ohi);
+                            }
+                        }
+                        continue;
+                    }
                     float lo[kW], hi[kW], olo[kW], ohi[kW];
                     unraw<T, kW>(rlo[j], lo);
                     unraw<T, kW>(rhi[j], hi);
@@ -207,7 +241,7 @@ rope_fwd_kernel(const T* __restrict__ qkv, const T* __restrict__ cosp, const T* 
 // Backward work item = (token, group, pass, p): pass 0 turns the group's q cotangents into dq (one output per
 // head), pass 1 / 2 fold the q_per_kv expanded copies of dk / dv into the single k / v slot (fp32 sum, rounded
 // once, as the expand's vjp does).  Passes are separate threads so their gathers overlap.
-template <typename T, int kW>
+template <typename T, int kW, bool kPk>
 __global__ void __launch_bounds__(128, 4)
 rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __restrict__ dv, const T* __restrict__ cosp,
                 const T* __restrict__ sinp, T* __restrict__ dqkv, RopeShape s, int64_t nitems) {
@@ -240,12 +274,18 @@ rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __r
         const int nsrc = pass == 0 ? s.qpk : (s.expand ? s.qpk : 1);
         const int head0 = pass == 0 ? g * s.qpk : (s.expand ? g * s.qpk : g);
         const bool roped = paired && pass < 2;
-        float clo[kW], chi[kW], slo[kW], shi[kW];
+        float clo[kPk ? 1 : kW], chi[kPk ? 1 : kW], slo[kPk ? 1 : kW], shi[kPk ? 1 : kW];
+        uint4 pclo, pchi, pslo, pshi;
         if (roped) {
-            ldv<T, kW>(cosp, t * s.rope_n + e0, clo, false);
-            ldv<T, kW>(cosp, t * s.rope_n + e1, chi, false);
-            ldv<T, kW>(sinp, t * s.rope_n + e0, slo, false);
-            ldv<T, kW>(sinp, t * s.rope_n + e1, shi, false);
+            if constexpr (kPk) {
+                pclo = ld_keep(cosp + t * s.rope_n + e0), pchi = ld_keep(cosp + t * s.rope_n + e1);
+                pslo = ld_keep(sinp + t * s.rope_n + e0), pshi = ld_keep(sinp + t * s.rope_n + e1);
+            } else {
+                ldv<T, kW>(cosp, t * s.rope_n + e0, clo, false);
+                ldv<T, kW>(cosp, t * s.rope_n + e1, chi, false);
+                ldv<T, kW>(sinp, t * s.rope_n + e0, slo, false);
+                ldv<T, kW>(sinp, t * s.rope_n + e1, shi, false);
+            }
         }
         float acc_lo[kW], acc_hi[kW];
 #pragma unroll
@@ -263,6 +303,26 @@ rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __r
 #pragma unroll
             for (int j = 0; j < kBwdChunk; ++j) {
                 if (s0 + j < nsrc) {
+                    if constexpr (kPk) {
+                        uint4 dlo = rlo[j].v, dhi = rhi[j].v;
+                        if (roped) {
+                            // d_lo = rnd(rnd(cos_lo * glo) + rnd(sin_hi * ghi)),  d_hi = rnd(rnd(cos_hi * ghi) - rnd(sin_lo * glo))
+                            dlo = pk_mul_mul_add<T, false>(pclo, rlo[j].v, pshi, rhi[j].v);
+                            dhi = pk_mul_mul_add<T, true>(pchi, rhi[j].v, pslo, rlo[j].v);
+                        }
+                        if (pass == 0) {
+                            T* dst = grp + static_cast<int64_t>(s0 + j) * s.hs;
+                            st_stream(dst + e0, dlo);
+                            if (paired) st_stream(dst + e1, dhi);
+                        } else {
+                            float fl[kW], fh[kW];
+                            Vec<T>::unpack(dlo, fl);
+                            Vec<T>::unpack(dhi, fh);
+#pragma unroll
+                            for (int e = 0; e < kW; ++e) acc_lo[e] += fl[e], acc_hi[e] += fh[e];
+                        }
+                        continue;
+                    }
                     float glo[kW], ghi[kW], dlo[kW], dhi[kW];
                     unraw<T, kW>(rlo[j], glo);
                     unraw<T, kW>(rhi[j], ghi);
@@ -295,6 +355,15 @@ rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __r
     }
 }
 
+// B200K_ROPE_PACKED=0 selects the fp32 form for 16-bit storage (bit-for-bit comparison in the tests).
+bool packed_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("B200K_ROPE_PACKED");
+        return !(e != nullptr && e[0] == '0');
+    }();
+    return on;
+}
+
 bool shape_ok(const RopeShape& s) {
     return s.B >= 0 && s.T >= 0 && s.G > 0 && s.qpk > 0 && s.hs > 0 && s.rope_n >= 0 && s.rope_n <= s.hs && s.rope_n % 2 == 0;
 }
@@ -313,21 +382,17 @@ int run(bool fwd, const void* a0, const void* a1, const void* a2, const void* co
     const int64_t want = (nitems + 127) / 128;
     const int64_t cap = static_cast<int64_t>(sm_count()) * 64;
     const int grid = static_cast<int>(want < cap ? want : cap);
-    if (fwd) {
-        if (vec)
-            rope_fwd_kernel<T, kE><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(cosp), static_cast<const T*>(sinp),
-                                                         static_cast<T*>(o0), static_cast<T*>(o1), static_cast<T*>(o2), s, nitems);
+    auto launch = [&](auto kernel_fwd, auto kernel_bwd) {
+        if (fwd)
+            kernel_fwd<<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(cosp), static_cast<const T*>(sinp),
+                                             static_cast<T*>(o0), static_cast<T*>(o1), static_cast<T*>(o2), s, nitems);
         else
-            rope_fwd_kernel<T, 1><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(cosp), static_cast<const T*>(sinp),
-                                                        static_cast<T*>(o0), static_cast<T*>(o1), static_cast<T*>(o2), s, nitems);
-    } else {
-        if (vec)
-            rope_bwd_kernel<T, kE><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
-                                                         static_cast<const T*>(cosp), static_cast<const T*>(sinp), static_cast<T*>(o0), s, nitems);
-        else
-            rope_bwd_kernel<T, 1><<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
-                                                        static_cast<const T*>(cosp), static_cast<const T*>(sinp), static_cast<T*>(o0), s, nitems);
-    }
+            kernel_bwd<<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
+                                             static_cast<const T*>(cosp), static_cast<const T*>(sinp), static_cast<T*>(o0), s, nitems);
+    };
+    if (vec && kE == 8 && packed_enabled()) launch(rope_fwd_kernel<T, kE, (kE == 8)>, rope_bwd_kernel<T, kE, (kE == 8)>);
+    else if (vec) launch(rope_fwd_kernel<T, kE, false>, rope_bwd_kernel<T, kE, false>);
+    else launch(rope_fwd_kernel<T, 1, false>, rope_bwd_kernel<T, 1, false>);
     return launch_status();
 }
 

@@ -73,3 +73,49 @@ def test_norm_preservation_property():
     q, k, v = ops.qkv_rope_fwd(qkv, cos, sin, nh, G, hs, hs)
     q_in = qkv.view(B, T, G, nh // G + 2, hs)[:, :, :, : nh // G].permute(0, 2, 3, 1, 4).reshape(B, nh, T, hs)
     torch.testing.assert_close(q.norm(dim=-1), q_in.norm(dim=-1), rtol=1e-5, atol=1e-5)
+
+
+_FP32_FORM = r"""
+import os, sys, torch
+os.environ["B200K_ROPE_PACKED"] = "0"
+sys.path[:0] = [sys.argv[1]]
+from b200ex import ops
+d = torch.load(sys.argv[2])
+c = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in d.items()}
+q, k, v = ops.qkv_rope_fwd(c["qkv"], c["cos"], c["sin"], *c["args"])
+dqkv = ops.qkv_rope_bwd(c["dq"], c["dk"], c["dv"], c["cos"], c["sin"], *c["args"])
+torch.save({"q": q.cpu(), "k": k.cpu(), "v": v.cpu(), "dqkv": dqkv.cpu()}, sys.argv[3])
+"""
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_packed_form_equals_the_fp32_form_bit_for_bit(tmp_path, dtype):
+    """16-bit storage runs the rotation on packed 2 x 16-bit multiplies / adds / subtracts (one rounding of the exact
+    result) instead of fp32-op-then-round; the two are claimed to give the same bits.  The fp32 form runs in a
+    second process (B200K_ROPE_PACKED=0 is read once per process); inputs span many exponents, including products
+    that are subnormal or overflow in fp16, and cos/sin beyond [-1, 1]."""
+    import os
+    import subprocess
+    import sys
+
+    from b200ex import ops
+
+    g = torch.Generator().manual_seed(17)
+    B, T, n_head, groups, hs, rope_n = 2, 96, 8, 2, 64, 48
+    wide = lambda *s: (torch.randn(*s, generator=g) * torch.exp2(torch.randint(-14, 12, s, generator=g).float())).to(dtype)
+    d = {"qkv": wide(B, T, (n_head + 2 * groups) * hs), "cos": wide(T, rope_n), "sin": wide(T, rope_n),
+         "dq": wide(B, n_head, T, hs), "dk": wide(B, n_head, T, hs), "dv": wide(B, n_head, T, hs), "args": (n_head, groups, hs, rope_n)}
+    src, dst = tmp_path / "in.pt", tmp_path / "out.pt"
+    torch.save(d, src)
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "lightning-thunder_b200")
+    subprocess.run([sys.executable, "-c", _FP32_FORM, pkg, str(src), str(dst)], check=True, timeout=300)
+    ref = torch.load(dst)
+    c = {k: (v.to(DEV) if isinstance(v, torch.Tensor) else v) for k, v in d.items()}
+    q, k, v = ops.qkv_rope_fwd(c["qkv"], c["cos"], c["sin"], *c["args"])
+    dqkv = ops.qkv_rope_bwd(c["dq"], c["dk"], c["dv"], c["cos"], c["sin"], *c["args"])
+    torch.cuda.synchronize()
+    for name, t in (("q", q), ("k", k), ("v", v), ("dqkv", dqkv)):
+        a, e = t.cpu().contiguous().view(torch.int16), ref[name].contiguous().view(torch.int16)
+        # NaN payloads may differ between the two forms (inf - inf); compare them as "both NaN"
+        both_nan = torch.isnan(t.cpu().float()) & torch.isnan(ref[name].float())
+        assert torch.equal(a[~both_nan], e[~both_nan]), f"{name}: {(a != e).sum().item()} of {a.numel()} words differ"
