@@ -57,6 +57,11 @@ class PyTreeSpec:
             self.num_leaves = sum(c.num_leaves for c in children_specs)
         self.num_nodes = 1 + sum(c.num_nodes for c in children_specs)
 
+    @property
+    def type(self):
+        """Container type of the root node (``None`` for a leaf), as optree.PyTreeSpec.type."""
+        return None if self.kind == "leaf" else (type(None) if self.kind == "none" else self.node_type)
+
     def children(self):
         return list(self.children_specs)
 

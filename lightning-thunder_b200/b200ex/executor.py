@@ -81,6 +81,56 @@ def _is_cuda_float(p, allow_bool=False) -> bool:
 # --------------------------------------------------------------------------------------------------
 # The executor
 # --------------------------------------------------------------------------------------------------
+def _torch_runs_whole(bsym: BoundSymbol) -> bool:
+    """Would the reference's torch executor run this (composite) bound symbol as ONE ATen call?"""
+    try:
+        from thunder.executors.torchex import ex as torch_ex
+
+        return bool(torch_ex.can_execute(bsym))
+    except Exception:
+        return False
+
+
+def _is_float_convert(b: BoundSymbol) -> bool:
+    return (
+        b.sym.id == PrimIDs.CONVERT_ELEMENT_TYPE
+        and isinstance(b.args[0], TensorProxy)
+        and isinstance(b.output, TensorProxy)
+        and dtypes.is_float_dtype(b.args[0].dtype)
+        and dtypes.is_float_dtype(b.output.dtype)
+    )
+
+
+def _drop_internal_roundings(bsyms: list[BoundSymbol], unit: BoundSymbol) -> list[BoundSymbol]:
+    """Rounding points follow the reference's torch executor: it rounds where IT launches a kernel.  A composite
+    ltorch op that it runs as one ATen call (``gelu``, ``hardsigmoid``, ... outside autograd) is computed in fp32
+    inside and rounded once, although its decomposition — what a fusion executor sees — is written with ltorch
+    ops that each round to the storage dtype.  So inside such a unit an ``f32 -> narrow -> f32`` round trip is
+    dropped: consumers of the re-widened value read the fp32 original (what nvfuserex's ``remove_redundant_casts``
+    does for whole fusions, nvfuserex_impl.py:2281-2434).  Under autograd the same op arrives decomposed at the top
+    level, every piece is its own unit, and every rounding stays — again what the torch executor does there."""
+    unit_outs = {p.name for p in unit.flat_proxy_outs}
+    prod: dict[str, BoundSymbol] = {}
+    swap: dict = {}
+    out: list[BoundSymbol] = []
+    for b in bsyms:
+        if swap and b.has_input(swap):
+            b = b.from_bsym_swap_proxies(swap, skip_inputs=False, skip_output=True)
+        if _is_float_convert(b):
+            y, z = b.args[0], b.output
+            inner = prod.get(y.name)
+            if (
+                inner is not None and _is_float_convert(inner) and y.name not in unit_outs
+                and inner.args[0].dtype == z.dtype and dtypes.to_dtype(y.dtype).bytes < dtypes.to_dtype(z.dtype).bytes
+            ):
+                swap[variableify(z)] = inner.args[0]
+                continue
+        for o in b.flat_proxy_outs:
+            prod[o.name] = b
+        out.append(b)
+    return out
+
+
 class B200Executor(FusionExecutor):
     _optimization_fuel: int | FUEL_LEVEL
 
@@ -122,6 +172,8 @@ class B200Executor(FusionExecutor):
         out: list[BoundSymbol] = []
         for s in bsym.subsymbols:
             out.extend(self.flatten(s))
+        if _torch_runs_whole(bsym):
+            out = _drop_internal_roundings(out, bsym)
         return out
 
     @staticmethod

@@ -95,6 +95,10 @@ def main():
             mkx = lambda grad: torch.randn(6, 32).to(dt).requires_grad_(grad)
             mkb = lambda grad: torch.randn(32).to(dt).requires_grad_(grad)
             specs, fw, bw = collect(fn, (mkx(False), mkb(False)))
+            # Outside autograd the torch executor runs gelu as ONE call (one rounding), so in 16-bit storage the region is a
+            # different program from the op-by-op chain the family kernel implements: it stays on the generic path.
+            if act == "gelu" and dt != torch.float32:
+                specs = []
             for spec in specs:
                 leaves = [n for n, _ in spec.leaves]
                 if sorted(leaves) == ["b", "x"] and len(spec.outputs) == 1:
