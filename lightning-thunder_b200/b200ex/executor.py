@@ -1014,6 +1014,13 @@ class B200Region:
                 n = self._resolve(a.name)
                 if n not in produced and n not in inputs:
                     inputs[n] = (_tdtype(a.dtype), tuple(a.shape))
+            if opname != "broadcast_in_dim":
+                # The reference's traces are not always shape-consistent (the vjp of an implicitly broadcast 0-d tensor
+                # keeps the broadcast shape under a 0-d proxy and leaves the reduction to autograd's sum-to-size):
+                # such a region is left to the torch executor, whose kernels follow the runtime shapes.
+                for a in b.flat_proxy_args:
+                    if isinstance(a, TensorProxy) and tuple(a.shape) != tuple(out.shape):
+                        raise PwUnsupported(f"{self.name}: {b.sym.name} has operand shape {tuple(a.shape)} but output shape {tuple(out.shape)}")
             if opname == "broadcast_in_dim":
                 a, shape, bdims = b.args
                 nodes.append(PwNode("broadcast_in_dim", out.name, _tdtype(out.dtype), tuple(out.shape), (r(a), tuple(bdims))))
@@ -1064,6 +1071,12 @@ def _native_for(spec) -> _Step | None:
             env[role_out["out"]] = ops.swiglu_fwd(env[role_in["a"]], env[role_in["b"]]).view(shape)
 
         return _Step("b200k_swiglu_fwd", run)
+    # The family kernels work in one storage dtype; a program with the same structure but a leaf or an output of
+    # another dtype (relu's autograd saves the BOOL mask `a > 0`, not the pre-activation) stays on the generic path.
+    dtype_of = {name: dt for name, dt, _ in spec.outputs}
+    dtype_of.update({name: dt for (name, _), dt in zip(spec.leaves, spec.leaf_dtypes)})
+    if len({dtype_of[n] for n in list(role_in.values()) + list(role_out.values())}) != 1:
+        return None
     if kind in ("bias_gelu_fwd", "bias_relu_fwd"):
         act = "gelu" if "gelu" in kind else "relu"
         want_pre = "pre" in role_out

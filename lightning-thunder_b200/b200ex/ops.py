@@ -75,7 +75,7 @@ def _contig(t):
 def _rows2d(t: torch.Tensor) -> torch.Tensor:
     """View as [rows, hidden]; makes a contiguous copy only if the layout is not already row-major."""
     t = t if t.is_contiguous() else t.contiguous()
-    return t.view(-1, t.shape[-1])
+    return t.view(-1, t.shape[-1]) if t.dim() > 0 else t.view(1, 1)
 
 
 def rmsnorm_fwd(x, residual, weight, eps: float):

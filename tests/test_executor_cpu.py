@@ -115,11 +115,21 @@ def test_qkv_split_rope_lookaside():
 
 
 def test_bias_activation_regions_route_to_the_native_kernels():
-    for act, fn in (("gelu", lambda x, b: F.gelu(x + b)), ("relu", lambda x, b: F.relu(x + b))):
-        fw, bw = _trace(fn, torch.randn(6, 32).to(torch.bfloat16).requires_grad_(True), torch.randn(32).to(torch.bfloat16).requires_grad_(True))
-        assert [k for _, ks in fusions(fw) for k in ks] == [f"b200k_bias_act_fwd[{act}]"]
-        # dx from the fused backward kernel, the bias gradient from its column sums (no second pass over dx)
-        assert [k for _, ks in fusions(bw) for k in ks] == [f"b200k_bias_act_bwd[{act}]", "b200k_colsum"]
+    mk = lambda *s: torch.randn(*s).to(torch.bfloat16).requires_grad_(True)
+    fw, bw = _trace(lambda x, b: F.gelu(x + b), mk(6, 32), mk(32))
+    assert [k for _, ks in fusions(fw) for k in ks] == ["b200k_bias_act_fwd[gelu]"]
+    # dx from the fused backward kernel, the bias gradient from its column sums (no second pass over dx)
+    assert [k for _, ks in fusions(bw) for k in ks] == ["b200k_bias_act_bwd[gelu]", "b200k_colsum"]
+    # relu under autograd saves the BOOL mask `a > 0`, not the pre-activation the family kernel works on: the region
+    # keeps the trace's dtypes and runs as a generic program (one launch forward, where(mask, g, 0) backward)
+    fw, bw = _trace(lambda x, b: F.relu(x + b), mk(6, 32), mk(32))
+    assert [k for _, ks in fusions(fw) for k in ks] == ["b200k_pointwise"]
+    assert [k for _, ks in fusions(bw) for k in ks] == ["b200k_pointwise", "b200k_colsum"]
+    # outside autograd there is nothing to save and relu(x + b) is the family kernel
+    jf = thunder.jit(lambda x, b: F.relu(x + b), executors=[b200.ex])
+    with pytest.raises(RuntimeError):
+        jf(torch.randn(6, 32).to(torch.bfloat16), torch.randn(32).to(torch.bfloat16))
+    assert [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks] == ["b200k_bias_act_fwd[relu]"]
 
 
 def test_generic_pointwise_region_with_broadcast():

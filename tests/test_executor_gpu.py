@@ -121,8 +121,11 @@ def test_bias_activation(act):
     fn = (lambda x, b: F.gelu(x + b)) if act == "gelu" else (lambda x, b: F.relu(x + b))
     res = _both(fn, [_mk(256, 768, seed=12, scale=1.5), _mk(768, seed=13)])
     jf = res[0][2]
-    assert [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks] == [f"b200k_bias_act_fwd[{act}]"]
-    assert [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks] == [f"b200k_bias_act_bwd[{act}]", "b200k_colsum"]
+    # gelu saves the pre-activation and runs on the family kernels; relu's autograd saves the bool mask, so its regions
+    # keep the trace's dtypes and run as generic programs (see _native_for)
+    fwd_kind, bwd_kind = (f"b200k_bias_act_fwd[{act}]", f"b200k_bias_act_bwd[{act}]") if act == "gelu" else ("b200k_pointwise", "b200k_pointwise")
+    assert [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks] == [fwd_kind]
+    assert [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks] == [bwd_kind, "b200k_colsum"]
     _compare(res, f"bias_{act}", ulp=lambda b: b.float().abs() * 4 + 2.0)
 
 

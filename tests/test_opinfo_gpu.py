@@ -111,6 +111,61 @@ def test_b200_vs_torch_reference(name, tag):
         pytest.xfail("the reference's torch executor fails the same samples: " + "; ".join(shared[:3]))
 
 
+def _grad_cases():
+    # every op of the sweep, not only the ones the reference flags `supports_grad` (that flag selects the ops of its
+    # finite-difference tests); samples the torch executor cannot differentiate are skipped at run time
+    for name in sorted(_OPS):
+        for tag in ("f32", "bf16"):
+            if _DTYPES[tag] in _OPS[name].dtypes():
+                yield pytest.param(name, tag, id=f"{name}-{tag}")
+
+
+def _fwd_bwd(op, execs, sample, seed):
+    """Forward + backward of one sample under an executor list: (outputs, grads w.r.t. every tensor that requires grad)."""
+    jf = thunder.jit(op.op, executors=execs, cache="no caching")
+    out = jf(*sample.args, **sample.kwargs)
+    flat = torch.utils._pytree.tree_leaves
+    outs = [o for o in flat(out) if isinstance(o, torch.Tensor) and o.requires_grad]
+    leaves = [a for a in flat((sample.args, sample.kwargs)) if isinstance(a, torch.Tensor) and a.requires_grad]
+    if not outs or not leaves:
+        return jf, out, None
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    cots = [torch.randn(o.shape, generator=g, device=DEV, dtype=torch.float32).to(o.dtype) for o in outs]
+    return jf, out, torch.autograd.grad(outs, leaves, grad_outputs=cots, allow_unused=True)
+
+
+@pytest.mark.parametrize("name,tag", list(_grad_cases()))
+def test_b200_vs_torch_executor_forward_backward(name, tag):
+    """Under autograd both executors run the same decomposed trace, so outputs and input gradients of the b200 regions
+    must agree with the torch executor's on the reference's samples (the pattern of thunder/tests/test_grad.py's
+    executor-consistency checks)."""
+    op, dt = _OPS[name], _DTYPES[tag]
+    default_comp, skip, _ = _directives(op, dt)
+    if skip:
+        pytest.skip(skip)
+    ran = 0
+    for i, sample in enumerate(op.sample_inputs(DEV, dt, requires_grad=True)):
+        if i >= 3:
+            break
+        try:
+            _, want_out, want_grads = _fwd_bwd(op, ["torch"], sample, i)
+        except Exception:
+            continue  # the reference's torch executor cannot differentiate this sample
+        jf, out, grads = _fwd_bwd(op, [b200.ex], sample, i)
+        comp = sample.comp if sample.comp is not None else default_comp
+        comp(out, want_out, equal_nan=True)
+        if want_grads is not None:
+            for g, w in zip(grads, want_grads):
+                if w is None:
+                    assert g is None
+                else:
+                    comp(g, w, equal_nan=True)
+        ran += 1
+    torch.cuda.synchronize()
+    if ran == 0:
+        pytest.skip("no differentiable sample")
+
+
 def test_zz_vocabulary_was_claimed():
     """Runs after the sweep: the ops below are the pointwise vocabulary b200 must fuse (not decline) for float CUDA
     tensors; a silent decline would make the sweep above a test of the torch executor."""
