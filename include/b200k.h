@@ -244,6 +244,19 @@ B200K_API int b200k_layernorm_bwd(const void* dy, const void* x, const void* wei
                         int64_t hidden, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Counter-based uniform random numbers — SURVEY §8 row f.1 (dropout masks).
+ * Replaces prims.uniform_philox (thunder/core/prims.py:3007-3045) as the reference's fusion executor evaluates it
+ * (thunder/executors/nvfuserex_impl.py:1147-1181), with the seed / offset pair of prims.get_and_update_rng_state
+ * (thunder/executors/torchex.py:478-493: offset = the generator's Philox offset / 4, advanced by one per call).
+ *   block(s) = Philox-4x32-10(key = seed, counter = (offset, subsequence s))              four 32-bit words
+ *   u(i)     = word (i % 4) of block(i / 4) * 2^-32 + 2^-33, with 1.0 mapped to 0.0      fp32 in [0, 1)
+ *   out[i]   = round_T(minval + (maxval - minval) * u(i)), a value that rounds to maxval becomes minval
+ * out: `numel` contiguous elements of `dtype`.  The same (seed, offset) always gives the same values, on any grid.
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_uniform_philox(void* out, int64_t numel, uint64_t seed, uint64_t offset, float minval, float maxval,
+                         int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Generic pointwise region — SURVEY §8 rows a3/a4.  Executes a fused region made only of elementwise
  * prims, convert_element_type and broadcast_in_dim (the claimable vocabulary of
  * thunder/executors/nvfuserex_impl.py:971-2514 restricted to pointwise work) as ONE pass over memory:

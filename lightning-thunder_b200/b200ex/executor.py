@@ -215,7 +215,13 @@ class B200Executor(FusionExecutor):
     # -- the pass (nvfuserex_impl.py:836-939) ---------------------------------------------------------
     def fusion_pass(self, trace: TraceCtx) -> TraceCtx:
         start = time.perf_counter_ns()
+        from thunder.core.rematerialization import replace_uniform
         from thunder.executors.data_dependent_partition import Node, consecutive_fusion, dataflow_fusion, fuse_bound_symbols
+
+        # `uniform` -> stateless `uniform_philox` + explicit generator-state updates, as nvfuserex does first thing
+        # (nvfuserex_impl.py:838-841): a dropout mask can then be regenerated in the backward from two integers instead
+        # of being saved.  The reference's `disable_replace_uniform` compile option is honoured inside.
+        trace = replace_uniform(trace)
 
         fusedtrace: TraceCtx = from_trace(trace)
         producers, consumers = utils.producers_and_consumers(trace)
@@ -474,6 +480,54 @@ ex.register_supported(b200_layer_norm_bwd.id)
 ex.register_supported(ltorch.layer_norm, _layer_norm_check, execution_transform=_layer_norm_transform, grad_transform=_layer_norm_grad)
 
 
+# ---- uniform_philox (dropout masks that the backward can regenerate from seed / offset) -------------
+def _uniform_philox_check(shape, minval, maxval, *, device, dtype, seed, offset) -> bool:
+    if device.devicetype is not thunder.core.devices.DeviceType.CUDA and not _CLAIM_CPU_FOR_TESTS:
+        return False
+    if _tdtype(dtype) not in (torch.float32, torch.bfloat16, torch.float16):
+        return False
+    if not all(isinstance(d, int) for d in shape) or not isinstance(minval, (int, float)) or not isinstance(maxval, (int, float)):
+        return False
+    # seed / offset come from prims.get_and_update_rng_state as host integers; tensor-valued ones stay with torch
+    return not isinstance(seed, TensorProxy) and not isinstance(offset, TensorProxy)
+
+
+def _uniform_philox_impl(shape, minval, maxval, *, device, dtype, seed, offset):
+    return ops.uniform_philox(
+        shape, minval, maxval, device=thunder.core.devices.to_torch_device(device), dtype=_tdtype(dtype), seed=seed, offset=offset
+    )
+
+
+ex.register_supported(PrimIDs.UNIFORM_PHILOX, _uniform_philox_check)
+
+
+def _uniform_check(shape, minval, maxval, *, device, dtype) -> bool:
+    # Claimed so that the prim reaches fusion_pass, where replace_uniform turns it into uniform_philox.  Real CUDA
+    # devices only: the generator-state prim that replace_uniform inserts does not exist for other devices.
+    if device.devicetype is not thunder.core.devices.DeviceType.CUDA:
+        return False
+    return _tdtype(dtype) in (torch.float32, torch.bfloat16, torch.float16) and all(isinstance(d, int) for d in shape)
+
+
+def _take_generator_state(device: torch.device) -> tuple[int, int]:
+    """(seed, offset / 4) of the device's default generator, which is then advanced by 4 — one call's worth in the
+    convention of prims.get_and_update_rng_state (torchex.py:478-493), so both spellings draw the same numbers."""
+    state = torch.cuda.get_rng_state(device)
+    seed, offset = (int(v) for v in state.view(torch.int64).tolist())
+    torch.cuda.set_rng_state(torch.tensor([seed, (offset // 4 + 1) * 4], dtype=torch.int64).view(torch.uint8), device)
+    return seed, offset // 4
+
+
+def _uniform_impl(shape, minval, maxval, *, device, dtype):
+    # only reached with the reference's `disable_replace_uniform` option: same numbers, state handled here
+    dev = thunder.core.devices.to_torch_device(device)
+    seed, offset = _take_generator_state(dev)
+    return ops.uniform_philox(shape, minval, maxval, device=dev, dtype=_tdtype(dtype), seed=seed, offset=offset)
+
+
+ex.register_supported(PrimIDs.UNIFORM, _uniform_check)
+
+
 # ---- cross-entropy ---------------------------------------------------------------------------------
 def _ce_fwd_meta(a, target, ignore_index, reduction):
     loss = TensorProxy(like=a, shape=())
@@ -664,6 +718,8 @@ _MACRO_IMPL: dict[Any, Callable] = {
     b200_rms_norm_bwd.id: _rms_norm_bwd_impl,
     b200_layer_norm_fwd.id: _layer_norm_fwd_impl,
     b200_layer_norm_bwd.id: _layer_norm_bwd_impl,
+    PrimIDs.UNIFORM_PHILOX: _uniform_philox_impl,
+    PrimIDs.UNIFORM: _uniform_impl,
     b200_cross_entropy_fwd.id: _ce_fwd_impl,
     b200_cross_entropy_bwd.id: _ce_bwd_impl,
     b200_qkv_split_rope.id: _rope_fwd_impl,

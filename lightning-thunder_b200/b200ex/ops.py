@@ -15,7 +15,7 @@ from . import _lib
 
 __all__ = [
     "rmsnorm_fwd", "rmsnorm_bwd", "swiglu_fwd", "swiglu_bwd", "cross_entropy_fwd", "cross_entropy_bwd",
-    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "colsum", "layernorm_fwd", "layernorm_bwd",
+    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "colsum", "layernorm_fwd", "layernorm_bwd", "uniform_philox",
     "ACT_CODE", "DTYPE_CODE",
 ]
 
@@ -320,4 +320,21 @@ def colsum(x):
         scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
         rc = L.b200k_colsum(_ptr(x2), _ptr(out), _ptr(scratch), nbytes, rows, hidden, _code(x), _stream(dev))
     _lib.check(rc, "b200k_colsum")
+    return out
+
+
+def uniform_philox(shape, minval: float, maxval: float, *, device, dtype: torch.dtype, seed: int, offset: int):
+    """Uniform random tensor in [minval, maxval) from (seed, offset) — see b200k_uniform_philox."""
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        raise RuntimeError("b200ex launchers take CUDA tensors only (there is no CPU path)")
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    out = torch.empty(tuple(shape), dtype=dtype, device=dev)
+    with _on(dev):
+        rc = _lib.lib().b200k_uniform_philox(
+            out.data_ptr(), out.numel(), int(seed) & 0xFFFFFFFFFFFFFFFF, int(offset) & 0xFFFFFFFFFFFFFFFF, float(minval), float(maxval),
+            _code(out), _stream(dev),
+        )
+    _lib.check(rc, "b200k_uniform_philox")
     return out

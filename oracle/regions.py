@@ -396,3 +396,54 @@ def layernorm_bwd(dy, x, weight, has_bias: bool, mean, rstd):
     if dt == torch.float32:
         return torch.add(direct, stats), dw, db
     return torch.add(direct.to(dt), stats.to(dt)), dw, db
+
+
+# ----------------------------------------------------------------------------------------------
+# Counter-based uniform random numbers — SURVEY §8 row f.1 (dropout)
+# ----------------------------------------------------------------------------------------------
+_PHILOX_M0, _PHILOX_M1 = 0xD2511F53, 0xCD9E8D57
+_PHILOX_W0, _PHILOX_W1 = 0x9E3779B9, 0xBB67AE85
+
+
+def philox4x32_10(seed: int, subsequence, counter: int):
+    """Philox-4x32-10 (Salmon et al., SC'11; the generator behind curand's Philox4_32_10 and ATen's CUDA RNG):
+    key = the 64-bit seed, 128-bit counter = (counter, subsequence).  ``subsequence`` is a numpy uint64 array; returns
+    a uint32 array [..., 4].  Ten rounds of ``(hi(M1*c2) ^ c1 ^ k0, lo(M1*c2), hi(M0*c0) ^ c3 ^ k1, lo(M0*c0))`` with the
+    key bumped by the Weyl constants between rounds."""
+    import numpy as np
+
+    sub = np.asarray(subsequence, dtype=np.uint64)
+    mask = np.uint64(0xFFFFFFFF)
+    c0 = np.full(sub.shape, counter & 0xFFFFFFFF, dtype=np.uint64)
+    c1 = np.full(sub.shape, (counter >> 32) & 0xFFFFFFFF, dtype=np.uint64)
+    c2, c3 = sub & mask, (sub >> np.uint64(32)) & mask
+    k0, k1 = seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+    for _ in range(10):
+        p0, p1 = np.uint64(_PHILOX_M0) * c0, np.uint64(_PHILOX_M1) * c2
+        c0, c1, c2, c3 = ((p1 >> np.uint64(32)) ^ c1 ^ np.uint64(k0)) & mask, p1 & mask, ((p0 >> np.uint64(32)) ^ c3 ^ np.uint64(k1)) & mask, p0 & mask
+        k0, k1 = (k0 + _PHILOX_W0) & 0xFFFFFFFF, (k1 + _PHILOX_W1) & 0xFFFFFFFF
+    return np.stack([c0, c1, c2, c3], axis=-1).astype(np.uint32)
+
+
+def uniform_philox(shape, minval: float, maxval: float, seed: int, offset: int, dtype):
+    """``prims.uniform_philox`` (thunder/core/prims.py:3007-3045) in the fusion executor's convention
+    (thunder/executors/nvfuserex_impl.py:1147-1181 and torchex.py:478-493, "the nvFuser way"): ``offset`` is the
+    generator's Philox offset divided by 4 and is used as the counter as it is; element ``i`` (row-major) takes
+    component ``i % 4`` of the block with subsequence ``i // 4``, so one call consumes a single counter value and the
+    state prim can advance the generator by 4 per call.  u = x * 2^-32 + 2^-33 in fp32 (curand_uniform), mapped from
+    (0, 1] to [0, 1), scaled to [minval, maxval) and rounded to ``dtype`` (a value that rounds up to maxval becomes minval)."""
+    import numpy as np
+
+    n = 1
+    for s in shape:
+        n *= int(s)
+    idx = np.arange(n, dtype=np.uint64)
+    blocks = philox4x32_10(int(seed), idx >> np.uint64(2), int(offset))
+    x = blocks[np.arange(n), (idx & np.uint64(3)).astype(np.int64)] if n else np.zeros(0, dtype=np.uint32)
+    u = x.astype(np.float32) * np.float32(2.0**-32) + np.float32(2.0**-33)
+    u = np.where(u == np.float32(1.0), np.float32(0.0), u).astype(np.float32)
+    lo, hi = np.float32(minval), np.float32(maxval)
+    v = (lo + (hi - lo) * u.astype(np.float64)).astype(np.float32) if (minval, maxval) != (0.0, 1.0) else u
+    t = torch.from_numpy(v).to(dtype)
+    t = torch.where(t == torch.tensor(maxval, dtype=dtype), torch.tensor(minval, dtype=dtype), t)
+    return t.reshape(tuple(shape))
