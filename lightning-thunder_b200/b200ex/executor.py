@@ -45,6 +45,7 @@ from thunder.executors.utils import Region
 from thunder.extend import FUEL_LEVEL, FusionExecutor, register_executor
 
 from . import ops
+from . import jit
 from .pointwise import PwLaunch, PwNode, PwUnsupported, compile_chain
 
 __all__ = ["ex", "B200Executor", "qkv_split_rope", "swiglu"]
@@ -819,7 +820,22 @@ class B200Region:
 
         absorbed: set[int] = set()
         macro_steps: dict[int, tuple] = {}  # id(bsym) -> (step, input names, output names)
+        # uniform_philox tensors that only feed pointwise work of this region are not launched at all: they become
+        # "generated" leaves of the consuming programs, produced in registers by the specialised kernels (and
+        # materialised by PwLaunch when a launch cannot use one).  name -> (shape, dtype, lo, hi, seed, offset)
+        self.generated: dict[str, tuple] = {}
         for b in live:
+            if b.sym.id == PrimIDs.UNIFORM_PHILOX and jit.enabled():
+                name = b.output.name
+                cons = consumers.get(name, [])
+                if name not in region_outs and cons and all(c.sym.id in _PW_OPNAME for c in cons):
+                    ref = lambda v: self._resolve(v.name) if isinstance(v, Proxy) else int(v)
+                    shape, lo, hi = b.args
+                    self.generated[name] = (tuple(shape), _tdtype(b.kwargs["dtype"]), float(lo), float(hi), ref(b.kwargs["seed"]), ref(b.kwargs["offset"]))
+                    absorbed.add(id(b))
+        for b in live:
+            if id(b) in absorbed:
+                continue
             if b.sym.id == PrimIDs.SUM:
                 macro_steps[id(b)] = self._colsum_step(b, prod, consumers, region_outs, absorbed)
                 continue
@@ -829,7 +845,7 @@ class B200Region:
             macro_steps[id(b)] = fused if fused is not None else self._macro_step(b)
 
         steps: list[_Step] = []
-        available = set(self.input_names)
+        available = set(self.input_names) | set(self.generated)
         remaining = [b for b in live if id(b) not in absorbed]
         while remaining:
             progressed = False
@@ -1084,14 +1100,16 @@ class B200Region:
                 nodes.append(PwNode("convert", out.name, _tdtype(out.dtype), tuple(out.shape), (r(b.args[0]),)))
             else:
                 nodes.append(PwNode(opname, out.name, _tdtype(out.dtype), tuple(out.shape), tuple(r(a) for a in b.args)))
-        specs = compile_chain(inputs, nodes, outs)  # PwUnsupported propagates: the fusion pass then declines the region
+        gen = {n: self.generated[n] for n in inputs if n in self.generated}
+        # PwUnsupported propagates: the fusion pass then declines the region
+        specs = compile_chain(inputs, nodes, outs, {n: (g[2], g[3]) for n, g in gen.items()})
         steps = []
         for spec in specs:
-            native = _native_for(spec)
+            native = _native_for(spec) if not gen else None
             if native is not None:
                 steps.append(native)
                 continue
-            launch = PwLaunch(spec)
+            launch = PwLaunch(spec, {n: g for n, g in gen.items() if any(n == leaf for leaf, _ in spec.leaves)})
 
             def run(env, launch=launch):
                 env.update(launch.run(env))

@@ -23,6 +23,7 @@ import threading
 import torch
 
 MAX_IN, MAX_OUT = 10, 6
+MAX_GEN = 4  # random leaves generated inside one kernel (two 64-bit scalars each)
 _lock = threading.Lock()
 _kernels: dict = {}
 _state = {"checked": False, "ok": False, "why": ""}
@@ -54,7 +55,7 @@ def enabled() -> bool:
 _SKELETON_HEAD = r"""
 typedef unsigned int u32; typedef unsigned short u16; typedef unsigned char u8; typedef long long i64;
 struct Op { void* ptr; i64 s0, s1; int inner; int dtype; };
-struct Params { i64 d0, d1, d2; Op in[%(MAX_IN)d]; Op out[%(MAX_OUT)d]; };
+struct Params { i64 d0, d1, d2; i64 sc[%(MAX_SC)d]; Op in[%(MAX_IN)d]; Op out[%(MAX_OUT)d]; };
 struct V4 { u32 x, y, z, w; };
 __device__ __forceinline__ V4 ldg16(const void* p) { V4 r; asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%%0,%%1,%%2,%%3}, [%%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p)); return r; }
 __device__ __forceinline__ void stg16(void* p, V4 v) { asm volatile("st.global.L1::no_allocate.v4.u32 [%%0], {%%1,%%2,%%3,%%4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
@@ -92,6 +93,18 @@ __device__ __forceinline__ void st_f16(const Op& t, i64 off, const float* r) { V
 __device__ __forceinline__ void st_bool(const Op& t, i64 off, const float* r) { u8* p = (u8*)t.ptr + off;
   #pragma unroll
   for (int i = 0; i < 8; ++i) p[i] = r[i] != 0.f ? 1 : 0; }
+// uniform_philox leaves (b200k_uniform_philox convention): elements li0 .. li0+7 of the row-major tensor are the two
+// Philox-4x32-10 blocks with subsequence li0/4 and li0/4 + 1, counter = offset, key = seed; u = x * 2^-32 + 2^-33, 1 -> 0
+__device__ __forceinline__ void philox_block(u32 k0, u32 k1, u32 c0, u32 c1, u32 c2, u32 c3, u32* w) {
+  #pragma unroll
+  for (int r = 0; r < 10; ++r) { const u32 h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0, h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+    c0 = h1 ^ c1 ^ k0; c1 = l1; c2 = h0 ^ c3 ^ k1; c3 = l0; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+  w[0] = c0; w[1] = c1; w[2] = c2; w[3] = c3; }
+__device__ __forceinline__ void gen_unit8(i64 seed, i64 offset, i64 li0, float* r) { u32 w[8]; const unsigned long long s = (unsigned long long)li0 >> 2;
+  philox_block((u32)seed, (u32)((unsigned long long)seed >> 32), (u32)offset, (u32)((unsigned long long)offset >> 32), (u32)s, (u32)(s >> 32), w);
+  philox_block((u32)seed, (u32)((unsigned long long)seed >> 32), (u32)offset, (u32)((unsigned long long)offset >> 32), (u32)(s + 1), (u32)((s + 1) >> 32), w + 4);
+  #pragma unroll
+  for (int i = 0; i < 8; ++i) { const float u = __fmaf_rn((float)w[i], 2.3283064365386963e-10f, 1.1641532182693481e-10f); r[i] = u == 1.0f ? 0.0f : u; } }
 """
 
 _DT = {torch.float32: "f32", torch.bfloat16: "bf16", torch.float16: "f16", torch.bool: "bool"}
@@ -110,13 +123,15 @@ _EXPR = {
 }
 
 
-def generate_source(spec, inner_flags: tuple, one_d: bool, unroll: int) -> str:
+def generate_source(spec, inner_flags: tuple, one_d: bool, unroll: int, in_kernel_rng: bool = True) -> str:
     """CUDA C for one program.  ``spec.ssa`` is the SSA list of the compiler; ``inner_flags[k]`` says whether input k
     is unit-stride (True) or broadcast (False) along the inner dimension."""
     n_in, n_out = len(spec.leaves), len(spec.outputs)
     in_dt = [_DT[dt] for dt in spec.leaf_dtypes]
     out_dt = [_DT[dt] for _, dt, _ in spec.outputs]
-    L = [_SKELETON_HEAD % {"MAX_IN": MAX_IN, "MAX_OUT": MAX_OUT}]
+    gen = (spec.generated or {}) if in_kernel_rng else {}
+    slot_of = {idx: slot for slot, idx in enumerate(sorted(gen))}
+    L = [_SKELETON_HEAD % {"MAX_IN": MAX_IN, "MAX_OUT": MAX_OUT, "MAX_SC": 2 * MAX_GEN}]
     L.append('extern "C" __global__ void __launch_bounds__(256) pw_kernel(const __grid_constant__ Params P) {')
     L.append("  const i64 d2v = P.d2 / 8, total = P.d0 * P.d1 * d2v;")
     L.append(f"  const i64 first = ((i64)blockIdx.x * blockDim.x) * {unroll} + threadIdx.x, step = (i64)gridDim.x * blockDim.x * {unroll};")
@@ -132,7 +147,14 @@ def generate_source(spec, inner_flags: tuple, one_d: bool, unroll: int) -> str:
         for k in range(n_in):
             L.append(f"    float v{u}_{k}[8];")
             off = f"i0_{u} * P.in[{k}].s0 + i1_{u} * P.in[{k}].s1"
-            if inner_flags[k]:
+            if k in gen:
+                lo, hi = gen[k]
+                rnd = {"bf16": "rnd_bf16", "f16": "rnd_f16"}.get(in_dt[k], "")
+                L.append(f"    if (live{u}) {{ gen_unit8(P.sc[{2 * slot_of[k]}], P.sc[{2 * slot_of[k] + 1}], (i0_{u} * P.d1 + i1_{u}) * P.d2 + i2_{u}, v{u}_{k});")
+                L.append("      #pragma unroll")
+                scale = "" if (lo, hi) == (0.0, 1.0) else f" x = __fmaf_rn({hi!r}f - {lo!r}f, x, {lo!r}f);"
+                L.append(f"      for (int e = 0; e < 8; ++e) {{ float x = v{u}_{k}[e];{scale} x = {rnd}(x); v{u}_{k}[e] = x == {hi!r}f ? {lo!r}f : x; }} }}")
+            elif inner_flags[k]:
                 L.append(f"    if (live{u}) ld_{in_dt[k]}(P.in[{k}], {off} + i2_{u}, v{u}_{k});")
             else:
                 L.append(f"    if (live{u}) {{ const float b = ld1(P.in[{k}], {off}); for (int e = 0; e < 8; ++e) v{u}_{k}[e] = b; }}")
@@ -168,7 +190,8 @@ class _Operand(ctypes.Structure):
 
 
 class Params(ctypes.Structure):
-    _fields_ = [("d0", ctypes.c_int64), ("d1", ctypes.c_int64), ("d2", ctypes.c_int64), ("inp", _Operand * MAX_IN), ("out", _Operand * MAX_OUT)]
+    _fields_ = [("d0", ctypes.c_int64), ("d1", ctypes.c_int64), ("d2", ctypes.c_int64), ("sc", ctypes.c_int64 * (2 * MAX_GEN)),
+                ("inp", _Operand * MAX_IN), ("out", _Operand * MAX_OUT)]
 
 
 def _check(res, what):
@@ -226,16 +249,17 @@ def unroll_for(n_in: int) -> int:
     return 4 if n_in <= 2 else (2 if n_in <= 4 else 1)
 
 
-def get_kernel(spec, inner_flags: tuple, one_d: bool, device_index: int) -> JitKernel:
-    key = (spec.signature, inner_flags, one_d, device_index)
+def get_kernel(spec, inner_flags: tuple, one_d: bool, device_index: int, in_kernel_rng: bool = True) -> JitKernel:
+    in_kernel_rng = bool(in_kernel_rng and spec.generated)
+    key = (spec.signature, inner_flags, one_d, device_index, in_kernel_rng)
     k = _kernels.get(key)
     if k is not None:
         return k
     with _lock:
         k = _kernels.get(key)
         if k is None:
-            unroll = unroll_for(len(spec.leaves))
-            src = generate_source(spec, inner_flags, one_d, unroll)
+            unroll = unroll_for(len(spec.leaves) - (len(spec.generated) if in_kernel_rng else 0))
+            src = generate_source(spec, inner_flags, one_d, unroll, in_kernel_rng)
             with torch.cuda.device(device_index):
                 k = JitKernel(compile_cubin(src), unroll)
             _kernels[key] = k

@@ -46,6 +46,7 @@ OPS = [
 ]
 OPCODE = {n: i for i, n in enumerate(OPS)}
 BINARY = {"add", "sub", "mul", "div", "pow", "maximum", "minimum", "gt", "ge", "lt", "le", "eq", "ne", "and", "or"}
+COMPARE = {"gt", "ge", "lt", "le", "eq", "ne"}
 UNARY = {"neg", "abs", "exp", "log", "sqrt", "rsqrt", "reciprocal", "erf", "tanh", "not", "sign", "floor", "ceil", "exp2", "log2",
          "log1p", "expm1", "sin", "cos", "erfc", "sigmoid", "trunc", "round"}
 # ops whose fp32 result is exactly representable whenever the operands are: no rounding instruction needed
@@ -81,6 +82,9 @@ class PwProgramSpec:
     ssa: list | None = None  # (op, a, b, c, imm) in evaluation order; what b200ex.jit turns into straight-line CUDA C
     out_ids: list | None = None
     leaf_dtypes: list | None = None
+    # leaf index -> (minval, maxval) for leaves that are counter-based random tensors spanning the whole iteration
+    # space: the specialised kernels generate them in registers instead of loading them (see PwLaunch.gen_info)
+    generated: dict | None = None
 
 
 class _Operand(ctypes.Structure):
@@ -107,8 +111,9 @@ def _f32_bits(x: float) -> int:
 # --------------------------------------------------------------------------------------------------
 # Compilation
 # --------------------------------------------------------------------------------------------------
-def compile_region(inputs: dict, nodes: list, outputs: list) -> list:
-    """inputs: name -> (dtype, shape); nodes in execution order; outputs: value names.
+def compile_region(inputs: dict, nodes: list, outputs: list, generated: dict | None = None) -> list:
+    """inputs: name -> (dtype, shape); nodes in execution order; outputs: value names; generated: input name ->
+    (minval, maxval) for inputs that are uniform_philox tensors (b200k_uniform_philox convention).
     Returns one :class:`PwProgramSpec` per distinct output shape.  Raises :class:`PwUnsupported`."""
     producer = {n.out: n for n in nodes}
     meta = {k: v for k, v in inputs.items()}
@@ -129,19 +134,19 @@ def compile_region(inputs: dict, nodes: list, outputs: list) -> list:
         best = None
         perms = itertools.permutations(outs) if len(outs) <= 3 else [tuple(outs)]
         for perm in perms:
-            spec = _compile_group(shape, list(perm), inputs, producer, meta)
+            spec = _compile_group(shape, list(perm), inputs, producer, meta, generated or {})
             if best is None or spec.signature < best.signature:
                 best = spec
         specs.append(best)
     return specs
 
 
-def compile_chain(inputs: dict, nodes: list, outputs: list) -> list:
+def compile_chain(inputs: dict, nodes: list, outputs: list, generated: dict | None = None) -> list:
     """Like :func:`compile_region`, but a region too large for one program (registers, code words, operand
     slots) is cut into consecutive programs that hand intermediates over through memory.  The returned
     specs must be launched in order."""
     try:
-        return compile_region(inputs, nodes, outputs)
+        return compile_region(inputs, nodes, outputs, generated)
     except PwUnsupported:
         if len(nodes) <= 1:
             raise
@@ -158,13 +163,13 @@ def compile_chain(inputs: dict, nodes: list, outputs: list) -> list:
     inputs_second = dict(inputs)
     inputs_second.update({o: meta_first[o] for o in outs_first})
     outs_second = [o for o in outputs if o in made_second]
-    specs = compile_chain(inputs, first, outs_first) if outs_first else []
+    specs = compile_chain(inputs, first, outs_first, generated) if outs_first else []
     if outs_second:
-        specs += compile_chain(inputs_second, second, outs_second)
+        specs += compile_chain(inputs_second, second, outs_second, generated)
     return specs
 
 
-def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
+def _compile_group(iter_shape, outs, inputs, producer, meta, generated) -> PwProgramSpec:
     ssa = []  # (op, a, b, c, imm)  operands are ssa ids
     memo: dict = {}
     leaves: list = []
@@ -213,6 +218,12 @@ def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
             return const(float(a))
         raise PwUnsupported(f"operand {a!r}")
 
+    def as_dtype(x, dt):
+        """A Python number as ATen sees it next to a tensor of dtype dt (rounded to 16-bit storage types)."""
+        if isinstance(x, (int, float)) and not isinstance(x, bool) and dt in (torch.bfloat16, torch.float16):
+            return float(torch.tensor(float(x), dtype=dt))
+        return x
+
     def rounded(r, n):
         if n.op in EXACT:
             return r
@@ -239,7 +250,8 @@ def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
         if n.op == "mov":
             return arg(n.args[0], mapping)
         if n.op == "where":
-            c, a, b = (arg(x, mapping) for x in n.args)
+            c = arg(n.args[0], mapping)
+            a, b = (arg(as_dtype(x, n.dtype), mapping) for x in n.args[1:])
             return emit("where", c, a, b)
         if n.op == "pow" and isinstance(n.args[1], (int, float)) and not isinstance(n.args[1], bool):
             # ATen evaluates small constant exponents by multiplication / sqrt (pow_tensor_scalar_optimized_kernel)
@@ -258,7 +270,15 @@ def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
                 return a
             return rounded(emit("pow", a, const(e)), n)
         if n.op in BINARY:
-            a, b = arg(n.args[0], mapping), arg(n.args[1], mapping)
+            x, y = n.args[0], n.args[1]
+            if n.op in COMPARE:
+                # ATen compares in the tensor operand's dtype: a Python number is cast to it first (a wrapped scalar does
+                # not take part in type promotion), so `u_bf16 < 0.9` tests against bf16(0.9).  Arithmetic ops get their
+                # scalar in fp32 (opmath), which is what the fp32 constant already is.
+                dts = [meta[v][0] for v in (x, y) if isinstance(v, str)]
+                if len(dts) == 1:
+                    x, y = as_dtype(x, dts[0]), as_dtype(y, dts[0])
+            a, b = arg(x, mapping), arg(y, mapping)
             return rounded(emit(n.op, a, b), n)
         if n.op in UNARY:
             return rounded(emit(n.op, arg(n.args[0], mapping)), n)
@@ -274,6 +294,11 @@ def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
     # covers counted from the innermost one
     nd = len(iter_shape)
     sig += "|" + ",".join(f"{meta[nm][0]}:" + ("*" if tuple(mp) == ident else "/".join(str(d - nd) for d in mp)) for nm, mp in leaves)
+    # random leaves that cover the iteration space one to one can be produced inside the kernel
+    gen = {i: tuple(float(v) for v in generated[nm]) for i, (nm, mp) in enumerate(leaves)
+           if nm in generated and tuple(mp) == ident and tuple(meta[nm][1]) == tuple(iter_shape)}
+    if gen:
+        sig += "|gen:" + ",".join(f"{i}:{lo!r}:{hi!r}" for i, (lo, hi) in sorted(gen.items()))
 
     # register allocation: leaves are preloaded into registers 0..n_in-1, everything else linear scan
     if len(leaves) > MAX_IN or len(outs) > MAX_OUT:
@@ -322,6 +347,7 @@ def _compile_group(iter_shape, outs, inputs, producer, meta) -> PwProgramSpec:
     outputs = [(o, meta[o][0], reg_of[oid]) for o, oid in zip(outs, out_ids)]
     spec = PwProgramSpec(tuple(iter_shape), leaves, code, max(n_reg, 1), outputs, hashlib.sha1(sig.encode()).hexdigest())
     spec.ssa, spec.out_ids, spec.leaf_dtypes = ssa, out_ids, [meta[nm][0] for nm, _ in leaves]
+    spec.generated = gen or None
     small = _encode_small(ssa, len(leaves), out_ids)
     if small is not None:
         spec.small_code, spec.small_out_reg = small
@@ -427,8 +453,12 @@ class PwLaunch:
     use_jit = True         # False: always interpret (b200k_pointwise), never specialise with NVRTC
     jit_failures: list = []
 
-    def __init__(self, spec: PwProgramSpec):
+    def __init__(self, spec: PwProgramSpec, gen_info: dict | None = None):
         self.spec = spec
+        # name -> (shape, dtype, minval, maxval, seed, offset) for leaves that are uniform_philox tensors; seed / offset
+        # are ints or names of host integers in `env`.  Such a leaf is generated inside the specialised kernel when the
+        # spec allows it (spec.generated) and that kernel serves the launch; otherwise it is materialised first.
+        self.gen_info = gen_info or {}
         self._plans: dict = {}
         self.plan_hits = 0
         self.plan_misses = 0
@@ -451,7 +481,7 @@ class PwLaunch:
         for d in range(nd - 1, -1, -1):
             contig[d] = acc
             acc *= shape[d]
-        in_strides = [self._leaf_strides(t, m, nd) for t, (_, m) in zip(tensors, spec.leaves)]
+        in_strides = [self._leaf_strides(t, m, nd) if t is not None else list(contig) for t, (_, m) in zip(tensors, spec.leaves)]
         cshape, cstrides = _collapse(shape, in_strides + [contig])
         contig_fix = False
         if len(cshape) > 3:
@@ -467,7 +497,7 @@ class PwLaunch:
         P.d0, P.d1, P.d2 = cshape
         P.n_in, P.n_out, P.n_code, P.n_reg = len(tensors), len(spec.outputs), len(spec.code), spec.n_reg
         for k, (t, st) in enumerate(zip(tensors, cstrides[:-1])):
-            P.inp[k] = _Operand(0, st[0], st[1], st[2], DTYPE_CODE[t.dtype])
+            P.inp[k] = _Operand(0, st[0], st[1], st[2], DTYPE_CODE[t.dtype if t is not None else spec.leaf_dtypes[k]])
         so = [cshape[1] * cshape[2], cshape[2], 1]  # outputs are freshly allocated, contiguous over the collapsed box
         for k, (name, dt, reg) in enumerate(spec.outputs):
             P.out[k] = _Operand(0, so[0], so[1], so[2], DTYPE_CODE[dt])
@@ -495,7 +525,9 @@ class PwLaunch:
         for st in ins:
             if st[2] not in (0, 1) or (st[2] == 1 and (st[0] % 8 or st[1] % 8)):
                 return
-        if tensors is not None and any(t.data_ptr() % 16 for t, st in zip(tensors, ins) if st[2] == 1):
+        if tensors is not None and any(t.data_ptr() % 16 for t, st in zip(tensors, ins) if st[2] == 1 and t is not None):
+            return
+        if spec.generated and len(spec.generated) > jit.MAX_GEN:
             return
         JP = jit.Params()
         JP.d0, JP.d1, JP.d2 = cshape
@@ -509,23 +541,41 @@ class PwLaunch:
         plan.jit_params = JP
         plan.items = cshape[0] * cshape[1] * (cshape[2] // 8)
 
-    def run(self, env: dict) -> dict:
+    def _materialise(self, name: str, env: dict, dev) -> torch.Tensor:
+        from . import ops
+
+        shape, dt, lo, hi, seed, offset = self.gen_info[name]
+        val = lambda v: env[v] if isinstance(v, str) else v
+        return ops.uniform_philox(shape, lo, hi, device=dev, dtype=dt, seed=val(seed), offset=val(offset))
+
+    def run(self, env: dict, _in_kernel_rng: bool = True) -> dict:
         spec = self.spec
         shape = spec.iter_shape
+        in_kernel = spec.generated if (spec.generated and _in_kernel_rng and self.use_jit and jit.enabled()) else {}
         tensors = []
-        for name, mapping in spec.leaves:
-            t = env[name]
+        dev = None
+        for idx, (name, mapping) in enumerate(spec.leaves):
+            if idx in in_kernel:
+                tensors.append(None)
+                continue
+            t = env.get(name)
+            if t is None and name in self.gen_info:
+                if dev is None:
+                    dev = next((v.device for v in env.values() if isinstance(v, torch.Tensor) and v.is_cuda), torch.device("cuda", torch.cuda.current_device()))
+                t = env[name] = self._materialise(name, env, dev)  # kept in env: other programs of the region reuse it
             if not isinstance(t, torch.Tensor) or not t.is_cuda:
                 raise RuntimeError(f"b200ex pointwise: operand {name} is not a CUDA tensor")
             if t.dim() != len(mapping):
                 raise RuntimeError(f"b200ex pointwise: operand {name} has rank {t.dim()}, expected {len(mapping)}")
             tensors.append(t)
-        dev = tensors[0].device if tensors else torch.device("cuda", torch.cuda.current_device())
+            dev = dev or t.device
+        if dev is None:
+            dev = next((v.device for v in env.values() if isinstance(v, torch.Tensor) and v.is_cuda), torch.device("cuda", torch.cuda.current_device()))
         outs = {name: torch.empty(shape, dtype=dt, device=dev) for name, dt, _ in spec.outputs}
         if 0 in shape:
             return outs
         # pointers enter the key only through their alignment class (vector path needs 16 B / 8 B alignment)
-        key = tuple((t.shape, t.stride(), t.dtype, t.data_ptr() % 16 == 0) for t in tensors)
+        key = tuple((t.shape, t.stride(), t.dtype, t.data_ptr() % 16 == 0) if t is not None else None for t in tensors)
         plan = self._plans.get(key)
         if plan is None:
             self.plan_misses += 1
@@ -534,6 +584,8 @@ class PwLaunch:
                 self._plans[key] = plan
         else:
             self.plan_hits += 1
+        if in_kernel and (plan.jit is None or plan.contig_fix):
+            return self.run(env, _in_kernel_rng=False)  # this descriptor is not served by a specialised kernel
         if plan.contig_fix:
             nd = len(shape)
             fixed = []
@@ -545,15 +597,21 @@ class PwLaunch:
             tensors = fixed
         if plan.jit is not None:
             try:
-                kernel = jit.get_kernel(spec, plan.jit[0], plan.jit[1], dev.index)
+                kernel = jit.get_kernel(spec, plan.jit[0], plan.jit[1], dev.index, bool(in_kernel))
             except jit.JitUnavailable as e:
                 plan.jit = None  # this host cannot build it: the interpreter below serves the descriptor instead
                 PwLaunch.jit_failures.append(str(e)[:400])
+                if in_kernel:
+                    return self.run(env, _in_kernel_rng=False)
             else:
                 with plan.lock:
                     JP = plan.jit_params
                     for k, t in enumerate(tensors):
-                        JP.inp[k].ptr = t.data_ptr()
+                        JP.inp[k].ptr = t.data_ptr() if t is not None else 0
+                    for slot, idx in enumerate(sorted(in_kernel)):
+                        _, _, _, _, seed, offset = self.gen_info[spec.leaves[idx][0]]
+                        JP.sc[2 * slot] = ctypes.c_int64((env[seed] if isinstance(seed, str) else seed) & 0xFFFFFFFFFFFFFFFF).value
+                        JP.sc[2 * slot + 1] = ctypes.c_int64((env[offset] if isinstance(offset, str) else offset) & 0xFFFFFFFFFFFFFFFF).value
                     for k, (name, _, _) in enumerate(spec.outputs):
                         JP.out[k].ptr = outs[name].data_ptr()
                     with _on(dev):

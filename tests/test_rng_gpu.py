@@ -98,9 +98,12 @@ def test_dropout_backward_regenerates_the_forward_mask():
     fw, bw = thunder.last_traces(jf)[-1], thunder.last_backward_traces(jf)[-1]
     names = [bs.sym.name for bs in fw.bound_symbols]
     assert "get_and_update_rng_state_impl" in names and "uniform" not in names  # stateless form, state prim outside
-    assert any("uniform_philox" in ks for _, ks in fusions(fw))
-    # nothing but the input and two integers is saved: the mask is regenerated in the backward region
-    assert any("uniform_philox" in ks for _, ks in fusions(bw))
+    # nothing but two integers is saved for the mask: the backward region contains the generator again
+    subsyms = lambda tr: [s.sym.name for bs in tr.bound_symbols if bs.sym.is_fusion for s in bs.subsymbols]
+    assert "uniform_philox" in subsyms(fw) and "uniform_philox" in subsyms(bw)
+    ret = next(bs for bs in fw.bound_symbols if bs.sym.name == "python_return")
+    saved_tensors = ret.args[1][0]
+    assert not any(tuple(getattr(p, "shape", ())) == (256, 1024) for p in saved_tensors), saved_tensors
     kept = y != 0
     torch.testing.assert_close(y[kept].float(), (x.detach()[kept].float() / (1 - p)).to(torch.bfloat16).float(), rtol=1.6e-2, atol=1e-5)
     # the gradient is 1/(1-p) exactly where the forward kept the element (zeros of x itself aside)
@@ -147,3 +150,52 @@ def test_uniform_philox_symbol_with_explicit_seed():
     out = jf((10, 30), thunder.float32, "cuda:0", 1234, 77)
     assert torch.equal(out.cpu(), O.uniform_philox((10, 30), 0.0, 1.0, 1234, 77, torch.float32))
     assert torch.equal(out, jf((10, 30), thunder.float32, "cuda:0", 1234, 77))
+
+
+@needs_thunder
+def test_dropout_is_one_kernel_and_equals_the_materialised_form():
+    """The mask never exists in memory: the region's specialised kernel generates the random numbers in registers.
+    The result must equal, bit for bit, the same region run with the random tensor materialised by
+    b200k_uniform_philox first (the path launches that cannot be specialised take)."""
+    from b200ex.pointwise import PwLaunch
+
+    x = torch.randn(512, 768, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    cot = torch.randn(512, 768, device=DEV, dtype=torch.bfloat16)
+    f = lambda x: F.dropout(F.gelu(x), 0.1) + x
+    res = {}
+    for fused in (True, False):
+        PwLaunch.use_jit = True
+        jf = thunder.jit(f, executors=[b200.ex])
+        torch.cuda.manual_seed(5)
+        if not fused:
+            orig = PwLaunch.run
+            PwLaunch.run = lambda self, env, _in_kernel_rng=True: orig(self, env, False)
+        try:
+            y = jf(x)
+            (g,) = torch.autograd.grad(y, x, cot)
+        finally:
+            if not fused:
+                PwLaunch.run = orig
+        res[fused] = (y.detach().clone(), g.clone())
+        if fused:
+            fw, bw = thunder.last_traces(jf)[-1], thunder.last_backward_traces(jf)[-1]
+            # forward: one launch (gelu, mask, scale, residual add together); the generator is not a launch of its own
+            assert [ks for _, ks in fusions(fw)] == [["b200k_pointwise"]], fusions(fw)
+            assert all(k != "uniform_philox" for _, ks in fusions(bw) for k in ks)
+    assert torch.equal(res[True][0], res[False][0]) and torch.equal(res[True][1], res[False][1])
+    dropped = (res[True][0] == x.detach()).float().mean().item()  # y == x exactly where the gelu branch was dropped
+    assert abs(dropped - 0.1) < 0.01
+
+
+@needs_thunder
+def test_dropout_with_unaligned_width_falls_back_to_the_materialised_mask():
+    x = torch.randn(33, 77, device=DEV, dtype=torch.bfloat16, requires_grad=True)  # 77 is not a multiple of 8
+    jf = thunder.jit(lambda x: F.dropout(x, 0.5), executors=[b200.ex])
+    torch.cuda.manual_seed(9)
+    y1 = jf(x)
+    torch.cuda.manual_seed(9)
+    y2 = jf(x)
+    assert torch.equal(y1, y2)
+    u = O.uniform_philox((33, 77), 0.0, 1.0, 9, 0, torch.bfloat16)
+    # thunder's dropout keeps an element where u < 1 - p (thunder/torch/__init__.py dropout)
+    assert torch.equal((y1 != 0).cpu() | (x.detach().cpu() == 0), (u < 0.5) | (x.detach().cpu() == 0))

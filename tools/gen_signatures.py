@@ -32,9 +32,9 @@ def collect(fn, args):
     captured = []
     orig = pointwise.PwLaunch.__init__
 
-    def spy(self, spec):
+    def spy(self, spec, *args, **kwargs):
         captured.append(spec)
-        orig(self, spec)
+        orig(self, spec, *args, **kwargs)
 
     pointwise.PwLaunch.__init__ = spy
     try:
