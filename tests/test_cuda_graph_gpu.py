@@ -17,7 +17,10 @@ def _step(ops, t):
     gx, gb = ops.bias_act_bwd(pre, None, t["dy"], "gelu", want_dbias=True)
     loss, rmax, rls, nv = ops.cross_entropy_fwd(t["x"], t["tgt"], -100)
     dl = ops.cross_entropy_bwd(t["g"], t["x"], t["tgt"], rmax, rls, nv, -100)
-    return [h, y, rstd, dx, dw, s, da, db, out, gx, gb, loss, dl]
+    ln, mean, lrstd = ops.layernorm_fwd(t["x"], t["w"], t["w"], 1e-5)
+    ldx, ldw, ldb = ops.layernorm_bwd(t["dy"], t["x"], t["w"], mean, lrstd, True)
+    u = ops.uniform_philox((256, 1024), 0.0, 1.0, device=DEV, dtype=torch.bfloat16, seed=3, offset=8)
+    return [h, y, rstd, dx, dw, s, da, db, out, gx, gb, loss, dl, ln, mean, lrstd, ldx, ldw, ldb, u]
 
 
 def test_launchers_replay_from_a_cuda_graph():
@@ -51,3 +54,48 @@ def test_launchers_replay_from_a_cuda_graph():
     for i, (a, b) in enumerate(zip(captured, fresh)):
         assert torch.equal(a, b), f"output {i} differs between graph replay and eager"
     assert not all(torch.equal(a, b) for a, b in zip(eager, fresh))  # the inputs really changed
+
+
+def test_reference_cudagraph_transform_over_b200_regions():
+    """thunder.transforms.cudagraph.CUDAGraphTransform captures the whole forward / backward trace —
+    our regions included — into CUDA graphs; replays on new input values must equal the un-graphed run."""
+    from thunder_env import import_thunder
+
+    try:
+        thunder, b200 = import_thunder()
+        from thunder.transforms.cudagraph import CUDAGraphTransform
+    except ImportError as e:  # pragma: no cover
+        pytest.skip(f"reference not importable: {e}")
+    import torch.nn.functional as F
+
+    class Block(torch.nn.Module):
+        def __init__(self, d=256):
+            super().__init__()
+            self.ln = torch.nn.LayerNorm(d)
+            self.fc, self.proj = torch.nn.Linear(d, 4 * d), torch.nn.Linear(4 * d, d)
+            self.w = torch.nn.Parameter(torch.ones(d))
+
+        def forward(self, x):
+            h = x + self.proj(F.gelu(self.fc(self.ln(x))))
+            return F.rms_norm(h, (h.shape[-1],), self.w, 1e-5)
+
+    torch.manual_seed(0)
+    model = Block().to(DEV).to(torch.bfloat16)
+    xs = [torch.randn(64, 256, device=DEV, dtype=torch.bfloat16) for _ in range(3)]
+    plain = thunder.jit(model, executors=[b200.ex])
+    graphed = thunder.jit(model, executors=[b200.ex], transforms=[CUDAGraphTransform()])
+    x_static = xs[0].clone().requires_grad_(True)
+    for x in xs:  # same input buffer, new values: what a training loop with static buffers does
+        with torch.no_grad():
+            x_static.copy_(x)
+        outs = []
+        for jm in (plain, graphed):
+            model.zero_grad(set_to_none=True)
+            x_static.grad = None
+            y = jm(x_static)
+            y.float().square().mean().backward()
+            outs.append((y.detach().clone(), x_static.grad.clone(), [p.grad.clone() for p in model.parameters()]))
+        (y0, g0, p0), (y1, g1, p1) = outs
+        assert torch.equal(y0, y1) and torch.equal(g0, g1)
+        for a, b in zip(p0, p1):
+            assert torch.equal(a, b)
