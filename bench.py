@@ -97,29 +97,47 @@ class Workload:
         b = self.bwd(self.sets[0], f)
         return {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in {**f, **b}.items()}
 
-    def e2e_step(self, host, device, out_host):
-        """One step from pinned host buffers: H2D of the forward inputs, forward, then the D2H of the forward's
-        results (side stream) overlaps the H2D of the backward-only inputs and the backward; PCIe is full duplex."""
-        main = torch.cuda.current_stream(device)
-        if not hasattr(self, "_side"):
-            self._side = torch.cuda.Stream(device)
-        side = self._side
-        d = {k: host[k].to(device, non_blocking=True) for k in self.fwd_inputs}
-        f = self.fwd(d)
-        ev = torch.cuda.Event()
-        ev.record(main)
-        side.wait_event(ev)
-        with torch.cuda.stream(side):
-            for k, v in f.items():
-                out_host[k].copy_(v, non_blocking=True)
-                v.record_stream(side)
-        for k in host:
-            if k not in d:
-                d[k] = host[k].to(device, non_blocking=True)
-        b = self.bwd(d, f)
-        for k, v in b.items():
-            out_host[k].copy_(v, non_blocking=True)
-        main.wait_stream(side)
+    def e2e_run(self, host, device, out_host, steps: int, stream):
+        """`steps` steps from pinned host buffers.  Every step copies its inputs host -> device, launches forward and
+        backward, copies every result device -> host and waits for them (the caller reads the step's results on the
+        host).  Three streams: a copy-in stream runs one step ahead of the compute stream, a copy-out stream drains
+        results behind it, so both PCIe directions stay busy; nothing is reused between steps."""
+        if not hasattr(self, "_h2d"):
+            self._h2d, self._d2h = torch.cuda.Stream(device), torch.cuda.Stream(device)
+        h2d, d2h = self._h2d, self._d2h
+        bwd_only = [k for k in host if k not in self.fwd_inputs]
+
+        def load(keys):
+            with torch.cuda.stream(h2d):
+                d = {k: host[k].to(device, non_blocking=True) for k in keys}
+                ev = torch.cuda.Event()
+                ev.record(h2d)
+            return d, ev
+
+        def drain(res):
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            d2h.wait_event(ev)
+            with torch.cuda.stream(d2h):
+                for k, v in res.items():
+                    out_host[k].copy_(v, non_blocking=True)
+
+        h2d.wait_stream(stream)
+        nxt = load(self.fwd_inputs)
+        for i in range(steps):
+            d, ev_f = nxt
+            late, ev_b = load(bwd_only)
+            if i + 1 < steps:
+                nxt = load(self.fwd_inputs)  # next step's inputs queue up behind this step's
+            stream.wait_event(ev_f)
+            f = self.fwd(d)
+            drain(f)
+            stream.wait_event(ev_b)
+            d.update(late)
+            b = self.bwd(d, f)
+            drain(b)
+            d2h.synchronize()  # this step's results are on the host
+        stream.wait_stream(d2h)
 
     def cpu_step_port(self):
         hi = self.host_inputs(0, pin=False)
@@ -639,6 +657,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train-step", action="store_true", help="skip the Llama-3-8B-shape training step that the default run appends as `train_step`")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="time the step loop through the Python launchers instead of per-step CUDA graphs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.workload == "llama_step":
@@ -692,12 +711,35 @@ def main():
     # ---- whole-step throughput, inputs resident in HBM ------------------------------------------
     for i in range(args.warmup):
         wl.step(i)
+    # One CUDA graph per buffer set, each holding one whole step (forward + backward launches): the timed loop
+    # replays them round-robin, so a step costs one graph launch on the host instead of three Python launchers —
+    # what the reference offers through CUDAGraphTransform.  --no-graph (or a failed capture) times the Python loop.
+    step_graphs, launch_mode = None, "python launchers, one call per kernel"
+    if not args.no_graph:
+        try:
+            torch.cuda.synchronize(device)
+            step_graphs = []
+            for i in range(NSETS):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    keep = wl.step(i)  # outputs stay alive with the graph
+                step_graphs.append((g, keep))
+            for g, _ in step_graphs:
+                g.replay()
+            torch.cuda.synchronize(device)
+            launch_mode = f"one CUDA graph per step ({NSETS} graphs, one per buffer set), replayed round-robin"
+        except Exception as e:
+            step_graphs, launch_mode = None, f"python launchers (graph capture failed: {type(e).__name__})"
     barrier()
     sampler.mark_load(True)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
-    for i in range(args.steps):
-        wl.step(i)
+    if step_graphs is not None:
+        for i in range(args.steps):
+            step_graphs[i % NSETS][0].replay()
+    else:
+        for i in range(args.steps):
+            wl.step(i)
     ev1.record(stream)
     barrier()
     ms = torch.tensor([ev0.elapsed_time(ev1)], device=device, dtype=torch.float64)
@@ -749,14 +791,11 @@ def main():
         host = wl.host_inputs(99 + rank, pin=True)
         out_host = wl.e2e_out_host()
         e2e_steps = max(3, min(args.steps, 20))
-        for _ in range(2):
-            wl.e2e_step(host, device, out_host)
+        wl.e2e_run(host, device, out_host, 2, stream)
         barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
-        for _ in range(e2e_steps):
-            wl.e2e_step(host, device, out_host)
-            stream.synchronize()  # the caller reads the step's result on the host
+        wl.e2e_run(host, device, out_host, e2e_steps, stream)
         b.record(stream)
         barrier()
         ems = torch.tensor([a.elapsed_time(b)], device=device, dtype=torch.float64)
@@ -765,7 +804,7 @@ def main():
         e2e = {"value": world * wl.bytes_per_step * e2e_steps / (ems.item() / 1e3) / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes,
                "ms_per_step": ems.item() / e2e_steps, "steps": e2e_steps,
-               "api": "b200ex.ops launchers on pinned host tensors (H2D + launch + D2H per step)"}
+               "api": "b200ex.ops launchers on pinned host tensors (H2D + launch + D2H of every result per step; copy-in one step ahead, copy-out behind)"}
 
     sampler.mark_load(False)
     clocks = sampler.stop() if rank == 0 else None
@@ -774,6 +813,7 @@ def main():
     train = None
     if not args.no_train_step and args.workload == "rmsnorm":
         wl.sets = wl.saved = None
+        step_graphs = None
         torch.cuda.empty_cache()
         try:
             thunder = import_reference()
@@ -803,7 +843,7 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": wl.describe(), "l2": f"inputs larger than L2: rotating {NSETS} buffer sets ({NSETS * wl.h2d_bytes / 1e9:.2f} GB of inputs)",
-                       "sharding": "each rank runs the region on its own micro-batch; no data-path collective"},
+                       "sharding": "each rank runs the region on its own micro-batch; no data-path collective", "launch": launch_mode},
             "roofline": {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbps"], "peak": peak, "unit": UNIT,
                          "frac": dom["achieved_gbps"] / peak, "frac_of_nominal_8TBps": dom["achieved_gbps"] / 8000.0,
                          "traffic": traffic, "traffic_source": "ncu --set full capture, profiles/r1_traffic.json" if traffic else None,
