@@ -68,9 +68,14 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
         execs = [sdpa_ex, "torch"]
     jm = thunder.jit(model, executors=execs, fusion_type=args.fusion_type)
     if world > 1:
-        from thunder.distributed import fsdp
+        from thunder.distributed import FSDPBucketingStrategy, fsdp
 
-        jm = fsdp(jm)
+        # the reference's own knob (thunder/distributed/__init__.py:337-350): NONE = one all-gather / reduce-scatter
+        # per parameter (227 each per step), BLOCK = one per transformer block
+        bucketing = {"none": FSDPBucketingStrategy.NONE, "layer": FSDPBucketingStrategy.LAYER, "block": FSDPBucketingStrategy.BLOCK}[
+            os.environ.get("B200_FSDP_BUCKETING", getattr(args, "fsdp_bucketing", "none"))
+        ]
+        jm = fsdp(jm, bucketing_strategy=bucketing)
     opt = torch.optim.AdamW(jm.parameters(), lr=1e-5, fused=True)
     # pinned host token buffers: the step's inputs cross PCIe every iteration, as a data loader would deliver them
     g = torch.Generator().manual_seed(99 + rank)

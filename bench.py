@@ -670,7 +670,9 @@ def main():
 
         if args.steps == 2000:
             args.steps, args.warmup = 5, 3
-        train_step.run(args, thunder, ClockSampler)
+        res = train_step.run(args, thunder, ClockSampler, emit=False)
+        if res is not None:  # rank 0
+            _emit(res)
         return
     wl = WORKLOADS[args.workload]()
     if os.environ.get("B200_BENCH_SHAPE") and hasattr(wl, "rows") and hasattr(wl, "hidden"):
