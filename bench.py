@@ -444,7 +444,51 @@ class LayerNorm(Workload):
         return (lambda x, w, b: F.layer_norm(x, (hidden,), w, b, eps)), ("x", "w", "b"), ("dy",)
 
 
-WORKLOADS = {"layernorm": LayerNorm, "rmsnorm": RmsnormResidual, "swiglu": Swiglu, "cross_entropy": CrossEntropy, "qkv_rope": QkvRope, "bias_gelu": BiasGelu}
+class Softmax(Workload):
+    """softmax over the last dimension of attention scores [2, 16, 2048, 2048] bf16: fwd reads x, writes y; bwd reads
+    dy and the saved y, writes dx."""
+
+    name = "softmax"
+    rows, hidden = 65536, 2048
+    launches_per_step = 2
+    fwd_inputs, bwd_inputs, bwd_saved = ("x",), ("dy",), ("y",)
+
+    def describe(self):
+        return f"softmax_fwd_bwd bf16 [{self.rows} rows x {self.hidden}] per GPU"
+
+    def out_nbytes(self):
+        t = self.rows * self.hidden * 2
+        return t, t
+
+    def saved_nbytes(self):
+        return self.rows * self.hidden * 2
+
+    def make(self, g, dev):
+        return dict(x=_randn(g, dev, self.rows, self.hidden, scale=2.0), dy=_randn(g, dev, self.rows, self.hidden))
+
+    def fwd(self, s):
+        from b200ex import ops
+
+        return dict(y=ops.softmax_fwd(s["x"]))
+
+    def bwd(self, s, f):
+        from b200ex import ops
+
+        return dict(dx=ops.softmax_bwd(s["dy"], f["y"]))
+
+    def oracle(self, hi):
+        from oracle import regions as O
+
+        y = O.softmax_fwd(hi["x"])
+        return y, O.softmax_bwd(hi["dy"], y)
+
+    def reference_fn(self):
+        import torch.nn.functional as F
+
+        return (lambda x: F.softmax(x, -1)), ("x",), ("dy",)
+
+
+WORKLOADS = {"softmax": Softmax, "layernorm": LayerNorm, "rmsnorm": RmsnormResidual, "swiglu": Swiglu, "cross_entropy": CrossEntropy, "qkv_rope": QkvRope, "bias_gelu": BiasGelu}
 
 
 # --------------------------------------------------------------------------------------------------

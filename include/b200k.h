@@ -244,6 +244,20 @@ B200K_API int b200k_layernorm_bwd(const void* dy, const void* x, const void* wei
                         int64_t hidden, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * softmax over the last dimension — SURVEY §8 row f.1.
+ * Forward replaces ltorch.softmax (thunder/torch/__init__.py `_softmax`), which the reference's torch executor runs
+ * as one torch.softmax call: fp32 inside, one rounding.
+ *   y = round_T(exp(f32(x) - max_j f32(x)) / sum_j exp(f32(x) - max_j f32(x)))
+ * Backward is the program autodiff derives for it, one storage-dtype rounding per op (mul, sum, sub, mul):
+ *   s  = round_T(sum_j round_T(y * dy))          fp32 accumulation inside the sum
+ *   dx = round_T(y * round_T(dy - s))
+ * x, y, dy, dx: [rows, cols] row-major contiguous of `dtype`.
+ * --------------------------------------------------------------------------------------------- */
+B200K_API int b200k_softmax_fwd(const void* x, void* y, int64_t rows, int64_t cols, int dtype, void* stream);
+B200K_API int b200k_softmax_bwd(const void* dy, const void* y, void* dx, int64_t rows, int64_t cols, int dtype,
+                      void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Counter-based uniform random numbers — SURVEY §8 row f.1 (dropout masks).
  * Replaces prims.uniform_philox (thunder/core/prims.py:3007-3045) as the reference's fusion executor evaluates it
  * (thunder/executors/nvfuserex_impl.py:1147-1181), with the seed / offset pair of prims.get_and_update_rng_state

@@ -481,6 +481,43 @@ ex.register_supported(b200_layer_norm_bwd.id)
 ex.register_supported(ltorch.layer_norm, _layer_norm_check, execution_transform=_layer_norm_transform, grad_transform=_layer_norm_grad)
 
 
+# ---- softmax over the last dimension ----------------------------------------------------------------
+def _softmax_fwd_meta(a):
+    return TensorProxy(like=a)
+
+
+def _softmax_bwd_meta(g, y):
+    return TensorProxy(like=y)
+
+
+b200_softmax_fwd = ex.register_operator("b200_softmax_fwd", meta=_softmax_fwd_meta, fn=ops.softmax_fwd, tags=[prims.OpTags.REDUCTION_OP])
+b200_softmax_bwd = ex.register_operator("b200_softmax_bwd", meta=_softmax_bwd_meta, fn=ops.softmax_bwd, tags=[prims.OpTags.REDUCTION_OP])
+
+
+def _softmax_check(a, /, dim, *, dtype=None) -> bool:
+    if not _is_cuda_float(a) or a.ndim < 1 or not isinstance(dim, int):
+        return False
+    if dim % a.ndim != a.ndim - 1 or a.shape[-1] == 0:
+        return False
+    return dtype is None or dtypes.to_dtype(dtype) == dtypes.to_dtype(a.dtype)
+
+
+def _softmax_transform(a, /, dim, *, dtype=None):
+    return b200_softmax_fwd(a)
+
+
+def _softmax_grad(a, /, dim, *, dtype=None):
+    y = b200_softmax_fwd(a)
+    put_grads((a,), (b200_softmax_bwd(get_grad(y), y),))
+    return y
+
+
+ex.register_supported(b200_softmax_fwd.id)
+ex.register_supported(b200_softmax_bwd.id)
+# the symbol is ltorch._softmax (id "torch.softmax"); torch.nn.functional.softmax is a plain wrapper around it
+ex.register_supported(ltorch._softmax, _softmax_check, execution_transform=_softmax_transform, grad_transform=_softmax_grad)
+
+
 # ---- uniform_philox (dropout masks that the backward can regenerate from seed / offset) -------------
 def _uniform_philox_check(shape, minval, maxval, *, device, dtype, seed, offset) -> bool:
     if device.devicetype is not thunder.core.devices.DeviceType.CUDA and not _CLAIM_CPU_FOR_TESTS:
@@ -720,6 +757,8 @@ _MACRO_IMPL: dict[Any, Callable] = {
     b200_layer_norm_fwd.id: _layer_norm_fwd_impl,
     b200_layer_norm_bwd.id: _layer_norm_bwd_impl,
     PrimIDs.UNIFORM_PHILOX: _uniform_philox_impl,
+    b200_softmax_fwd.id: ops.softmax_fwd,
+    b200_softmax_bwd.id: ops.softmax_bwd,
     PrimIDs.UNIFORM: _uniform_impl,
     b200_cross_entropy_fwd.id: _ce_fwd_impl,
     b200_cross_entropy_bwd.id: _ce_bwd_impl,

@@ -15,7 +15,7 @@ from . import _lib
 
 __all__ = [
     "rmsnorm_fwd", "rmsnorm_bwd", "swiglu_fwd", "swiglu_bwd", "cross_entropy_fwd", "cross_entropy_bwd",
-    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "colsum", "layernorm_fwd", "layernorm_bwd", "uniform_philox",
+    "qkv_rope_fwd", "qkv_rope_bwd", "bias_act_fwd", "bias_act_bwd", "colsum", "layernorm_fwd", "layernorm_bwd", "uniform_philox", "softmax_fwd", "softmax_bwd",
     "ACT_CODE", "DTYPE_CODE",
 ]
 
@@ -338,3 +338,27 @@ def uniform_philox(shape, minval: float, maxval: float, *, device, dtype: torch.
         )
     _lib.check(rc, "b200k_uniform_philox")
     return out
+
+
+def softmax_fwd(x):
+    """softmax over the last dimension — see b200k_softmax_fwd."""
+    dev = _require_cuda(x)
+    xc = _contig(x)
+    cols = xc.shape[-1]
+    y = torch.empty_like(xc)
+    with _on(dev):
+        rc = _lib.lib().b200k_softmax_fwd(xc.data_ptr(), y.data_ptr(), xc.numel() // cols if cols else 0, cols, _code(x), _stream(dev))
+    _lib.check(rc, "b200k_softmax_fwd")
+    return y
+
+
+def softmax_bwd(dy, y):
+    """dx of softmax over the last dimension from the saved output — see b200k_softmax_bwd."""
+    dev = _require_cuda(dy, y)
+    gc, yc = _contig(dy), _contig(y)
+    cols = yc.shape[-1]
+    dx = torch.empty_like(yc)
+    with _on(dev):
+        rc = _lib.lib().b200k_softmax_bwd(gc.data_ptr(), yc.data_ptr(), dx.data_ptr(), yc.numel() // cols if cols else 0, cols, _code(y), _stream(dev))
+    _lib.check(rc, "b200k_softmax_bwd")
+    return dx

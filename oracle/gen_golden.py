@@ -201,6 +201,14 @@ def case_layernorm(gen, dtype, rows, hidden, eps=1e-5, bias=True):
     return {"inputs": {**ins, "dy": dy}, "outputs": outs, "meta": {"eps": eps, "bias": bias}}
 
 
+def case_softmax(gen, dtype, rows, cols):
+    x = _rand(gen, (rows, cols), dtype, 2.0)
+    g = _rand(gen, (rows, cols), dtype)
+    (y,), gr = _run_ref(lambda x: F.softmax(x, -1), {"x": x}, ["x"], [g])
+    _same(O.softmax_fwd(x), y, "softmax y"), _same(O.softmax_bwd(g, y), gr["x"], "softmax dx")
+    return {"inputs": {"x": x, "g": g}, "outputs": {"y": y, "dx": gr["x"]}, "meta": {}}
+
+
 def main():
     gen = torch.Generator().manual_seed(20261106)
     cases = {}
@@ -229,6 +237,10 @@ def main():
     cases["layernorm_bf16_5x768"] = case_layernorm(gen, torch.bfloat16, 5, 768)
     cases["layernorm_bf16_7x100_nobias"] = case_layernorm(gen, torch.bfloat16, 7, 100, bias=False)  # unaligned hidden
     cases["layernorm_f32_3x1000"] = case_layernorm(gen, torch.float32, 3, 1000, eps=1e-6)
+    for name, dt in DT.items():
+        cases[f"softmax_{name}_16x256"] = case_softmax(gen, dt, 16, 256)
+    cases["softmax_bf16_5x1024"] = case_softmax(gen, torch.bfloat16, 5, 1024)
+    cases["softmax_bf16_7x100"] = case_softmax(gen, torch.bfloat16, 7, 100)  # unaligned width -> generic kernel
 
     out = os.path.join(ROOT, "tests", "golden", "regions.pt")
     os.makedirs(os.path.dirname(out), exist_ok=True)

@@ -37,6 +37,10 @@ __all__ = [
     "cross_entropy_bwd",
     "layernorm_fwd",
     "layernorm_bwd",
+    "softmax_fwd",
+    "softmax_bwd",
+    "philox4x32_10",
+    "uniform_philox",
 ]
 
 
@@ -447,3 +451,19 @@ def uniform_philox(shape, minval: float, maxval: float, seed: int, offset: int, 
     t = torch.from_numpy(v).to(dtype)
     t = torch.where(t == torch.tensor(maxval, dtype=dtype), torch.tensor(minval, dtype=dtype), t)
     return t.reshape(tuple(shape))
+
+
+# ----------------------------------------------------------------------------------------------
+# softmax over the last dimension — SURVEY §8 row f.1
+# ----------------------------------------------------------------------------------------------
+def softmax_fwd(x):
+    """ltorch.softmax (thunder/torch/__init__.py `_softmax`): the torch executor runs it as one ``torch.softmax`` call."""
+    return torch.softmax(x, -1)
+
+
+def softmax_bwd(g, y):
+    """Backward as autodiff derives it from the decomposition and the torch executor runs it: four torch calls on
+    storage-dtype tensors (``mul``, ``sum(keepdim)``, ``sub``, ``mul``), each rounding its result."""
+    t = torch.mul(y, g)
+    s = torch.sum(t, -1, True, dtype=None)
+    return torch.mul(y, torch.sub(g, s))

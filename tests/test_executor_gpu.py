@@ -80,6 +80,20 @@ def test_layer_norm(dtype, bias):
     _compare(res, f"layer_norm {dtype}", ulp=lambda b: b.float().abs() * (1.0 if dtype is BF else 16.0) + 8.0, grad_atol=0 if dtype is BF else 2e-5)
 
 
+@pytest.mark.parametrize("dtype", [BF, F32])
+def test_softmax_with_scale_and_mask(dtype):
+    def f(q, k):
+        att = (q @ k.transpose(-2, -1)) * 0.125
+        att = att.masked_fill(torch.ones(96, 96, device=q.device, dtype=torch.bool).tril().logical_not(), float("-inf"))
+        return F.softmax(att, dim=-1)
+
+    res = _both(f, [_mk(2, 4, 96, 64, dtype=dtype, seed=31), _mk(2, 4, 96, 64, dtype=dtype, seed=32)])
+    jf = res[0][2]
+    assert "b200_softmax_fwd" in [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks]
+    assert "b200_softmax_bwd" in [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks]
+    _compare(res, f"softmax {dtype}", ulp=lambda b: b.float().abs() * 4 + 1.0, grad_atol=0 if dtype is BF else 2e-5)
+
+
 def test_swiglu_inline_expression():
     res = _both(lambda a, b: F.silu(a) * b, [_mk(128, 1024, seed=4, scale=2.0), _mk(128, 1024, seed=5)])
     kinds = [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
@@ -291,6 +305,7 @@ def test_tiny_gpt2_forward_backward():
     bk = [k for _, ks in fusions(thunder.last_backward_traces(jm)[-1]) for k in ks]
     assert "b200_cross_entropy_fwd" in fk and "b200_cross_entropy_bwd" in bk
     assert fk.count("b200_layer_norm_fwd") == 5 and bk.count("b200_layer_norm_bwd") == 5
+    assert fk.count("b200_softmax_fwd") == 2 and bk.count("b200_softmax_bwd") == 2
     torch.testing.assert_close(results["b200"][0].float(), results["torch"][0].float(), rtol=1.6e-2, atol=1e-5)
     for n, g in results["b200"][1].items():
         ref = results["torch"][1][n]

@@ -27,7 +27,7 @@ DEV = "cuda"
 MAX_SAMPLES = 8
 _OTHER = (
     "where", "clamp", "lerp", "addcmul", "addcdiv", "masked_fill", "type_as", "to", "gelu", "layer_norm", "rms_norm",
-    "cross_entropy", "zeros_like", "ones_like", "full_like", "expand", "unsqueeze", "squeeze", "sum", "mean",
+    "cross_entropy", "softmax", "log_softmax", "dropout", "zeros_like", "ones_like", "full_like", "expand", "unsqueeze", "squeeze", "sum", "mean",
 )
 _OPS = {o.name: o for o in _opinfos.opinfos if o.name in _OTHER and o.torch_reference is not None}
 _OPS.update({o.name: o for o in list(_opinfos.elementwise_unary_ops) + list(_opinfos.elementwise_binary_ops) if o.torch_reference is not None})
