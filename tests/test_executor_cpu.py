@@ -48,6 +48,28 @@ def test_cpu_tensors_are_not_claimed_by_default():
     assert out.shape == (4, 8) and fusions(thunder.last_traces(jf)[-1]) == []
 
 
+def test_readme_mlp_on_cpu_is_the_reference_bit_for_bit():
+    """BASELINE.json configs[0]: the reference's README MLP (Linear 2048->4096, ReLU, Linear 4096->64, batch 64, fp32)
+    on the CPU.  b200 claims nothing there, so with b200 in the executor list the model must give exactly what the
+    reference's torch executor gives, forward and backward."""
+    b200._testing_claim_cpu(False)
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(2048, 4096), torch.nn.ReLU(), torch.nn.Linear(4096, 64))
+    x = torch.randn(64, 2048)
+    outs = []
+    for execs in ([b200.ex], ["torch"]):
+        model.zero_grad(set_to_none=True)
+        jm = thunder.jit(model, executors=execs)
+        y = jm(x)
+        y.square().mean().backward()
+        outs.append((y.detach().clone(), [p.grad.clone() for p in model.parameters()]))
+        if execs != ["torch"]:
+            assert fusions(thunder.last_traces(jm)[-1]) == []
+    (y0, g0), (y1, g1) = outs
+    assert torch.equal(y0, y1) and all(torch.equal(a, b) for a, b in zip(g0, g1))
+    torch.testing.assert_close(y0, model(x), rtol=1e-5, atol=1e-6)
+
+
 def test_rmsnorm_residual_and_swiglu_regions():
     bf = torch.bfloat16
 

@@ -311,3 +311,85 @@ def test_tiny_gpt2_forward_backward():
         ref = results["torch"][1][n]
         err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
         assert err.item() < 2e-2, f"grad {n}: relative error {err.item():.3e}"
+
+
+def test_readme_mlp_fp32_on_the_gpu():
+    """BASELINE.json configs[0] moved to the GPU: the bias + ReLU between the two linears and its backward are b200
+    regions; loss and gradients against the torch executor at the fp32 tolerance."""
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(2048, 4096), torch.nn.ReLU(), torch.nn.Linear(4096, 64)).to(DEV)
+    x = torch.randn(64, 2048, device=DEV)
+    outs = []
+    for execs in ([b200.ex], ["torch"]):
+        model.zero_grad(set_to_none=True)
+        jm = thunder.jit(model, executors=execs)
+        y = jm(x)
+        y.square().mean().backward()
+        outs.append((y.detach().clone(), [p.grad.clone() for p in model.parameters()], jm))
+    assert fusions(thunder.last_traces(outs[0][2])[-1]) and fusions(thunder.last_backward_traces(outs[0][2])[-1])
+    torch.testing.assert_close(outs[0][0], outs[1][0], rtol=1e-5, atol=1e-6)
+    for a, b in zip(outs[0][1], outs[1][1]):
+        torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
+
+
+def _grads_close(results, tol=2e-2):
+    for n, g in results["b200"][1].items():
+        ref = results["torch"][1][n]
+        err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
+        assert err.item() < tol, f"grad {n}: relative error {err.item():.3e}"
+
+
+def test_reference_llama2_model():
+    """thunder/tests/llama2_model.py (the llama2.c-style Transformer of the reference's own test-suite: RMSNorm spelled
+    with pow/mean/rsqrt, rotary embedding on real pairs, SwiGLU, masked softmax attention): loss and parameter
+    gradients with b200 against the torch executor."""
+    from thunder.tests import llama2_model
+
+    args = llama2_model.ModelArgs(dim=128, n_layers=2, n_heads=4, n_kv_heads=2, vocab_size=256, multiple_of=32, max_seq_len=64, dropout=0.0)
+    torch.manual_seed(0)
+    model = llama2_model.Transformer(args).to(DEV).to(BF)
+    ids = torch.randint(0, 256, (2, 64), device=DEV)
+    tgt = torch.randint(0, 256, (2, 64), device=DEV)
+    results = {}
+    for name, execs in (("b200", [b200.ex]), ("torch", ["torch"])):
+        model.zero_grad(set_to_none=True)
+        jm = thunder.jit(model, executors=execs)
+        logits = jm(ids, tgt)
+        loss = F.cross_entropy(logits.float().view(-1, logits.size(-1)), tgt.view(-1))  # outside the jitted module in this model
+        loss.backward()
+        results[name] = (loss.detach().clone(), {n: p.grad.detach().clone() for n, p in model.named_parameters() if p.grad is not None}, jm)
+    torch.cuda.synchronize()
+    fk = [k for _, ks in fusions(thunder.last_traces(results["b200"][2])[-1]) for k in ks]
+    assert fk.count("b200k_swiglu_fwd") == args.n_layers and len(fk) > 10
+    torch.testing.assert_close(results["b200"][0].float(), results["torch"][0].float(), rtol=1.6e-2, atol=1e-5)
+    _grads_close(results)
+
+
+def test_reference_bart_self_attention():
+    """thunder/tests/hf_bart_self_attn.py (the reference's copy of HF BART's attention block: scaled q, bmm, softmax,
+    dropout 0, bmm, biased projections)."""
+    from thunder.tests import hf_bart_self_attn
+
+    torch.manual_seed(0)
+    model = hf_bart_self_attn.BartAttention(256, 8, dropout=0.0).to(DEV).to(BF)
+    x = torch.randn(4, 96, 256, device=DEV, dtype=BF)
+    cot = torch.randn(4, 96, 256, device=DEV, dtype=BF)
+    mask = torch.zeros(4, 1, 96, 96, device=DEV, dtype=BF)
+    mask[:, :, :, 80:] = -10000.0  # padded keys
+    results = {}
+    for name, execs in (("b200", [b200.ex]), ("torch", ["torch"])):
+        model.zero_grad(set_to_none=True)
+        xx = x.clone().requires_grad_(True)
+        jm = thunder.jit(model, executors=execs)
+        out = jm(xx, mask)
+        y = out[0] if isinstance(out, (tuple, list)) else out
+        y.backward(cot)
+        grads = {n: p.grad.detach().clone() for n, p in model.named_parameters()}
+        grads["x"] = xx.grad.detach().clone()
+        results[name] = (y.detach().clone(), grads, jm)
+    torch.cuda.synchronize()
+    fk = [k for _, ks in fusions(thunder.last_traces(results["b200"][2])[-1]) for k in ks]
+    assert "b200_softmax_fwd" in fk
+    err = (results["b200"][0].float() - results["torch"][0].float()).norm() / results["torch"][0].float().norm()
+    assert err.item() < 1e-2
+    _grads_close(results)
