@@ -76,7 +76,16 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
             os.environ.get("B200_FSDP_BUCKETING", getattr(args, "fsdp_bucketing", "none"))
         ]
         jm = fsdp(jm, bucketing_strategy=bucketing)
-    opt = torch.optim.AdamW(jm.parameters(), lr=1e-5, fused=True)
+    # b200 arm: the multi-tensor AdamW kernel of this repo (b200ex.optim.AdamW, same arithmetic and state layout as
+    # torch's fused AdamW, which the reference's benchmark uses); B200_TORCH_ADAMW=1 or the torch arm: torch's own.
+    if args.executor == "b200" and os.environ.get("B200_TORCH_ADAMW", "0") != "1":
+        from b200ex.optim import AdamW
+
+        opt = AdamW(jm.parameters(), lr=1e-5)
+        optimizer_name = "b200ex.optim.AdamW (b200k_adamw)"
+    else:
+        opt = torch.optim.AdamW(jm.parameters(), lr=1e-5, fused=True)
+        optimizer_name = "torch.optim.AdamW(fused=True)"
     # pinned host token buffers: the step's inputs cross PCIe every iteration, as a data loader would deliver them
     g = torch.Generator().manual_seed(99 + rank)
     host = [
@@ -129,7 +138,7 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
             "metric": "llama3_8b_train_tokens_per_s", "value": tokens_per_s, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"llama_step: LitGPT-style Llama-3-8B shape, n_layer={cfg.n_layer}, micro-batch {B} x seq {T} per GPU, AdamW(fused), "
+            "config": {"workload": f"llama_step: LitGPT-style Llama-3-8B shape, n_layer={cfg.n_layer}, micro-batch {B} x seq {T} per GPU, {optimizer_name}, "
                                    f"{'fsdp ZeRO-2 (thunder.distributed.fsdp, NCCL)' if world > 1 else 'single GPU'}",
                        "executors": [str(e) if isinstance(e, str) else e.name for e in execs], "fusion_type": args.fusion_type,
                        "params": n_params},

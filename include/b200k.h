@@ -244,6 +244,31 @@ B200K_API int b200k_layernorm_bwd(const void* dy, const void* x, const void* wei
                         int64_t hidden, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Multi-tensor AdamW / Adam step — SURVEY §8 row f.4 (the optimizer step next to the fused regions).
+ * Replaces torch.optim.AdamW(fused=True) as the reference's training benchmark uses it
+ * (thunder/benchmarks/benchmark_litgpt.py:278-282), i.e. ATen's _fused_adamw_: per element, with the scalar
+ * hyper-parameters narrowed to fp32 as there,
+ *   p -= lr * weight_decay * p                               (decoupled; else g += p * weight_decay)
+ *   m  = beta1 * m + (1 - beta1) * g,   v = beta2 * v + (1 - beta2) * g * g
+ *   p -= (lr / bias_correction1) * m / (sqrt(v) / bias_correction2_sqrt + eps)          all in fp32
+ * p, m, v are rounded to `dtype` on store.  table: DEVICE array of tensors (all of `dtype`, 16-byte aligned);
+ * chunk_tensor / chunk_index: DEVICE arrays of n_chunks entries listing every chunk of b200k_adamw_chunk_elems(dtype)
+ * elements of every tensor (tensor index, chunk number within the tensor).  bias_correction1 = 1 - beta1^step,
+ * bias_correction2_sqrt = sqrt(1 - beta2^step), computed by the caller in double and narrowed to float.
+ * --------------------------------------------------------------------------------------------- */
+typedef struct {
+    void* param;
+    const void* grad;
+    void* exp_avg;
+    void* exp_avg_sq;
+    int64_t numel;
+} b200k_adam_tensor;
+B200K_API int64_t b200k_adamw_chunk_elems(int dtype);
+B200K_API int b200k_adamw(const b200k_adam_tensor* table, const int32_t* chunk_tensor, const int32_t* chunk_index,
+                int64_t n_chunks, double lr, double beta1, double beta2, double eps, double weight_decay,
+                float bias_correction1, float bias_correction2_sqrt, int decoupled_weight_decay, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * softmax over the last dimension — SURVEY §8 row f.1.
  * Forward replaces ltorch.softmax (thunder/torch/__init__.py `_softmax`), which the reference's torch executor runs
  * as one torch.softmax call: fp32 inside, one rounding.

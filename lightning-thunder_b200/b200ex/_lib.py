@@ -47,6 +47,8 @@ EXPORTS: dict[str, tuple] = {
     "b200k_layernorm_fwd": (c_int, [c_void_p] * 6 + [c_int64, c_int64, c_float, c_int, c_void_p]),
     "b200k_layernorm_bwd_scratch_bytes": (c_int64, [c_int64, c_int64]),
     "b200k_layernorm_bwd": (c_int, [c_void_p] * 9 + [c_int64, c_int64, c_int64, c_int, c_void_p]),
+    "b200k_adamw_chunk_elems": (c_int64, [c_int]),
+    "b200k_adamw": (c_int, [c_void_p, c_void_p, c_void_p, c_int64] + [ctypes.c_double] * 5 + [c_float, c_float, c_int, c_int, c_void_p]),
     "b200k_softmax_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "b200k_softmax_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "b200k_uniform_philox": (c_int, [c_void_p, c_int64, ctypes.c_uint64, ctypes.c_uint64, c_float, c_float, c_int, c_void_p]),
@@ -54,7 +56,7 @@ EXPORTS: dict[str, tuple] = {
     "b200k_pointwise": (c_int, [c_void_p, c_void_p]),
 }
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 _lock = threading.Lock()
 _lib = None

@@ -1,7 +1,7 @@
 // Library-level entry points: version, error strings, device queries.
 #include "common.cuh"
 
-extern "C" int b200k_version(void) { return 5; }
+extern "C" int b200k_version(void) { return 6; }
 
 extern "C" int b200k_sm_count(void) { return b200k::sm_count(); }
 

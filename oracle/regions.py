@@ -39,6 +39,7 @@ __all__ = [
     "layernorm_bwd",
     "softmax_fwd",
     "softmax_bwd",
+    "adamw_step",
     "philox4x32_10",
     "uniform_philox",
 ]
@@ -467,3 +468,27 @@ def softmax_bwd(g, y):
     t = torch.mul(y, g)
     s = torch.sum(t, -1, True, dtype=None)
     return torch.mul(y, torch.sub(g, s))
+
+
+# ----------------------------------------------------------------------------------------------
+# AdamW step — SURVEY §8 row f.4
+# ----------------------------------------------------------------------------------------------
+def adamw_step(p, g, m, v, step: int, lr: float, beta1: float, beta2: float, eps: float, weight_decay: float):
+    """One ``torch.optim.AdamW(fused=True)`` update (the optimizer of thunder/benchmarks/benchmark_litgpt.py:278-282),
+    i.e. ATen's ``_fused_adamw_``: every hyper-parameter is narrowed to fp32, the whole update is fp32, parameters and
+    moments are rounded to their storage dtype on store.  Returns (p, m, v) as new tensors."""
+    import numpy as np
+
+    dt = p.dtype
+    f = np.float32
+    arr = lambda t: t.detach().float().cpu().numpy().astype(np.float32)
+    P, G, M, V = arr(p), arr(g), arr(m), arr(v)
+    if weight_decay != 0:
+        P = P - (f(lr) * f(weight_decay)) * P
+    M = f(beta1) * M + (f(1) - f(beta1)) * G
+    V = f(beta2) * V + ((f(1) - f(beta2)) * G) * G
+    step_size = f(lr) / f(1 - beta1**step)
+    denom = np.sqrt(V) / f(math.sqrt(1 - beta2**step)) + f(eps)
+    P = P - (step_size * M) / denom
+    back = lambda a: torch.from_numpy(a.astype(np.float32)).to(dt)
+    return back(P), back(M), back(V)
