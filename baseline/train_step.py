@@ -60,12 +60,20 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
         model = GPT(cfg).to(torch.bfloat16)
     n_params = sum(p.numel() for p in model.parameters())
     cos, sin = build_rope_cache(T, cfg.rope_n_elem, base=cfg.rope_base, device=device, dtype=torch.bfloat16)
+    # attention is a library kernel in both arms: cuDNN's fused attention unless B200_ATTENTION=flash (baseline/attention.py)
+    attn = [sdpa_ex]
+    attention_name = "ATen flash attention (sdpa executor)"
+    if os.environ.get("B200_ATTENTION", "cudnn") == "cudnn":
+        from baseline.attention import cudnn_sdpa_ex
+
+        attn = [cudnn_sdpa_ex, sdpa_ex]
+        attention_name = "cuDNN fused attention through ATen (baseline/attention.py), both arms"
     if args.executor == "b200":
         import b200ex.executor as b200
 
-        execs = [sdpa_ex, b200.ex]
+        execs = attn + [b200.ex]
     else:
-        execs = [sdpa_ex, "torch"]
+        execs = attn + ["torch"]
     jm = thunder.jit(model, executors=execs, fusion_type=args.fusion_type)
     if world > 1:
         from thunder.distributed import FSDPBucketingStrategy, fsdp
@@ -138,7 +146,7 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
             "metric": "llama3_8b_train_tokens_per_s", "value": tokens_per_s, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"llama_step: LitGPT-style Llama-3-8B shape, n_layer={cfg.n_layer}, micro-batch {B} x seq {T} per GPU, {optimizer_name}, "
+            "config": {"workload": f"llama_step: LitGPT-style Llama-3-8B shape, n_layer={cfg.n_layer}, micro-batch {B} x seq {T} per GPU, {optimizer_name}, attention: {attention_name}, "
                                    f"{'fsdp ZeRO-2 (thunder.distributed.fsdp, NCCL)' if world > 1 else 'single GPU'}",
                        "executors": [str(e) if isinstance(e, str) else e.name for e in execs], "fusion_type": args.fusion_type,
                        "params": n_params},
