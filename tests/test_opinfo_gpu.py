@@ -13,15 +13,12 @@ from thunder_env import fusions, import_thunder
 
 pytestmark = pytest.mark.gpu
 
-try:
-    thunder, b200 = import_thunder()
-    import thunder.core.dtypes as dtypes
-    from thunder.core.pytree import tree_flatten, tree_map
-    from thunder.tests import opinfos as _opinfos
-    from thunder.tests.framework import assert_closer
-    from thunder.tests.opinfos import custom_comparator
-except ImportError as e:  # pragma: no cover
-    pytest.skip(f"reference not importable: {e}", allow_module_level=True)
+thunder, b200 = import_thunder()  # raises when baseline/_ref is missing: the plugin path must not skip silently
+import thunder.core.dtypes as dtypes
+from thunder.core.pytree import tree_flatten, tree_map
+from thunder.tests import opinfos as _opinfos
+from thunder.tests.framework import assert_closer
+from thunder.tests.opinfos import custom_comparator
 
 DEV = "cuda"
 MAX_SAMPLES = 8

@@ -1,5 +1,6 @@
-"""Makes the unmodified reference importable for the plugin tests: baseline/_ref (pip --target install that
-travels with the repo) or /root/reference (build container only), plus the dependency shims."""
+"""Makes the unmodified reference importable for the plugin tests: baseline/_ref (the pip --target install that
+``__graft_entry__.build()`` creates and that travels with the repo snapshot) plus the dependency shims.  Nothing here
+reads /root/reference: that tree exists in the build container only."""
 
 import os
 import sys
@@ -8,16 +9,19 @@ import warnings
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+class ReferenceMissing(RuntimeError):
+    """baseline/_ref is absent.  Deliberately not an ImportError, so no caller mistakes it for an optional import."""
+
+
 def import_thunder():
-    """Returns (thunder, b200 executor module) or raises ImportError."""
+    """Returns (thunder, b200 executor module); raises ReferenceMissing when baseline/_ref was never built."""
     shims = os.path.join(ROOT, "baseline", "shims")
-    ref = None
-    for cand in (os.path.join(ROOT, "baseline", "_ref"), "/root/reference"):
-        if os.path.isdir(os.path.join(cand, "thunder")):
-            ref = cand
-            break
-    if ref is None:
-        raise ImportError("reference thunder not found (baseline/_ref missing): pip --target install described in DESIGN.md")
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isfile(os.path.join(ref, "thunder", "__init__.py")):
+        raise ReferenceMissing(
+            "baseline/_ref/thunder not found: run `python -c 'import __graft_entry__ as g; g.build()'` in the build "
+            "container (it installs the reference there; the directory ships with the snapshot)"
+        )
     for p in (ref, shims, os.path.join(ROOT, "lightning-thunder_b200"), ROOT):
         if p not in sys.path:
             sys.path.insert(0, p)
