@@ -46,6 +46,7 @@ from thunder.extend import FUEL_LEVEL, FusionExecutor, register_executor
 
 from . import ops
 from . import jit
+from . import regionc
 from .pointwise import PwLaunch, PwNode, PwUnsupported, compile_chain
 
 __all__ = ["ex", "B200Executor", "qkv_split_rope", "swiglu"]
@@ -209,9 +210,27 @@ class B200Executor(FusionExecutor):
             flat: list[BoundSymbol] = []
             for b in bsyms:
                 flat.extend(self.flatten(b))
-            return all(b.sym.id in _MACRO_IMPL or b.sym.id in _PW_OPNAME or b.sym.id == PrimIDs.SUM for b in flat)
+            return all(b.sym.id in _MACRO_IMPL or b.sym.id in _PW_OPNAME or b.sym.id in _RC_PRIMS for b in flat)
         except AssertionError:
             return False
+
+    def _elementwise_runs(self, bsyms: list[BoundSymbol]):
+        """Consecutive runs of `bsyms`, flagged True when the run has no layout / reduction prim of the region
+        compiler (and is more than a shape-only group)."""
+        def plain(b):
+            try:
+                return all(x.sym.id in _MACRO_IMPL or x.sym.id in _PW_OPNAME or _is_leading_sum(x) for x in self.flatten(b))
+            except AssertionError:
+                return False
+
+        runs: list = []
+        for b in bsyms:
+            f = plain(b)
+            if runs and runs[-1][1] == f:
+                runs[-1][0].append(b)
+            else:
+                runs.append(([b], f))
+        return [(r, f and not all(_all_tagged(b, prims.OpTags.SHAPE_OP) for b in r)) for r, f in runs]
 
     # -- the pass (nvfuserex_impl.py:836-939) ---------------------------------------------------------
     def fusion_pass(self, trace: TraceCtx) -> TraceCtx:
@@ -265,16 +284,36 @@ class B200Executor(FusionExecutor):
                 try:
                     fused.append(self.fuse(region, counter))
                     counter += 1
-                except PwUnsupported:
-                    fused.extend(bsyms)  # decline: the torch executor runs these
+                except PwUnsupported as e:
+                    if os.environ.get("B200EX_DEBUG"):
+                        print(f"[b200ex] group of {len(bsyms)} bound symbols not lowered as one region: {e}", flush=True)
+                    # decline.  A group that only failed because of its layout / reduction prims keeps its purely
+                    # elementwise runs as fusions (what b200 claimed before it knew those prims); the rest goes to
+                    # the torch executor.
+                    for run, fusible in self._elementwise_runs(bsyms):
+                        if fusible and self.get_fuel():
+                            try:
+                                fused.append(self.fuse(Region(producers, consumers, run), counter))
+                                counter += 1
+                                continue
+                            except PwUnsupported:
+                                pass
+                        fused.extend(run)
             else:
                 fused.extend(bsyms)
         fusedtrace.bound_symbols = fused
 
+        # rematerialisation moves cheap producers into consuming regions, after which every fusion is rebuilt
+        # (update_fusion_call_ctx calls fuse again).  Should a rebuilt region no longer lower, keep the regions as
+        # they were partitioned: those did.
+        done = None
         if self._use_rematerialization:
-            fusedtrace = rematerialize(fusedtrace)
-        fusedtrace = dce(fusedtrace)
-        fusedtrace = update_fusion_call_ctx(fusedtrace)
+            try:
+                done = update_fusion_call_ctx(dce(rematerialize(fusedtrace)))
+            except PwUnsupported as e:
+                if os.environ.get("B200EX_DEBUG"):
+                    print(f"[b200ex] regions kept as partitioned, a rematerialised one did not lower: {e}", flush=True)
+        fusedtrace = done if done is not None else update_fusion_call_ctx(dce(fusedtrace))
         ms = (time.perf_counter_ns() - start) // 1000000
         fusedtrace.set_provenance(TraceProvenance(f"b200 fusion (took {ms} milliseconds)"))
         return fusedtrace
@@ -346,8 +385,6 @@ def _sum_check(a, dims) -> bool:
         return False
 
 
-ex.register_supported(PrimIDs.SUM, _sum_check)
-
 for _pid in _PW_OPNAME:
     if _pid is PrimIDs.CONVERT_ELEMENT_TYPE:
         ex.register_supported(_pid, _convert_check)
@@ -355,6 +392,86 @@ for _pid in _PW_OPNAME:
         ex.register_supported(_pid, _broadcast_check)
     else:
         ex.register_supported(_pid, _pw_check)
+
+
+# --------------------------------------------------------------------------------------------------
+# Layout prims and reductions (reshape / transpose / slice / pad / cat / squeeze / full and
+# sum / amax / amin / prod / var / var_mean, nvfuserex_impl.py:1071-1401, 2132-2244).  They are lowered by
+# b200ex.regionc: layout prims become index maps on the loads (no bytes moved, as in the oracle where they are
+# views), trailing-dim reductions make the kernel row-persistent, leading-dim sums are folded from per-CTA partials.
+# --------------------------------------------------------------------------------------------------
+def _ints(xs) -> bool:
+    return all(isinstance(x, int) and not isinstance(x, Proxy) for x in xs)
+
+
+def _rc_tensor(a) -> bool:
+    return isinstance(a, TensorProxy) and _is_cuda_float(a, allow_bool=True) and a.ndim <= regionc.MAX_RANK and _ints(a.shape)
+
+
+def _reshape_check(a, shape) -> bool:
+    return _rc_tensor(a) and _ints(shape)
+
+
+def _transpose_check(a, permutation) -> bool:
+    return _rc_tensor(a) and _ints(permutation)
+
+
+def _slice_check(a, start_indices, end_indices, strides=None) -> bool:
+    return _rc_tensor(a) and _ints(start_indices) and _ints(end_indices) and (strides is None or (_ints(strides) and all(s > 0 for s in strides)))
+
+
+def _pad_check(a, padding_value, padding_config) -> bool:
+    return _rc_tensor(a) and _pw_scalar_ok(padding_value) and all(_ints(c) and c[2] == 0 for c in padding_config)
+
+
+def _cat_check(tensors, dim) -> bool:
+    return len(tensors) > 0 and all(_rc_tensor(t) for t in tensors) and isinstance(dim, int) and len({t.dtype for t in tensors}) == 1
+
+
+def _full_check(shape, fill_value, *, device, dtype) -> bool:
+    if device.devicetype is not thunder.core.devices.DeviceType.CUDA and not _CLAIM_CPU_FOR_TESTS:
+        return False
+    return _ints(shape) and len(shape) <= regionc.MAX_RANK and _pw_scalar_ok(fill_value) and _tdtype(dtype) is not None
+
+
+def _squeeze_check(a, dims) -> bool:
+    return _rc_tensor(a) and _ints(dims)
+
+
+def _reduce_check(a, dims, **kwargs) -> bool:
+    # like the reference's _reduction_check (nvfuserex_impl.py:2112-2115): tensors of at least fp32 — ltorch upcasts
+    # 16-bit inputs before it reduces, so that is what arrives here
+    if not (_rc_tensor(a) and _tdtype(a.dtype) is torch.float32 and _ints(dims) and len(dims) > 0):
+        return False
+    corr = kwargs.get("correction", 0)
+    return isinstance(corr, (int, float)) and not isinstance(corr, Proxy)
+
+
+_RC_PRIMS: dict[Any, str] = {
+    PrimIDs.RESHAPE: "reshape", PrimIDs.TRANSPOSE: "transpose", PrimIDs.SLICE: "slice", PrimIDs.PAD: "pad", PrimIDs.CAT: "cat",
+    PrimIDs.FULL: "full", PrimIDs.SQUEEZE: "squeeze", PrimIDs.SUM: "sum", PrimIDs.AMAX: "amax", PrimIDs.AMIN: "amin",
+    PrimIDs.PROD: "prod", PrimIDs.VAR: "var", PrimIDs.VAR_MEAN: "var_mean",
+}
+
+ex.register_supported(PrimIDs.RESHAPE, _reshape_check)
+ex.register_supported(PrimIDs.TRANSPOSE, _transpose_check)
+ex.register_supported(PrimIDs.SLICE, _slice_check)
+ex.register_supported(PrimIDs.PAD, _pad_check)
+ex.register_supported(PrimIDs.CAT, _cat_check)
+ex.register_supported(PrimIDs.FULL, _full_check)
+ex.register_supported(PrimIDs.SQUEEZE, _squeeze_check)
+ex.register_supported(PrimIDs.SUM, lambda a, dims: _sum_check(a, dims) or _reduce_check(a, dims))
+for _pid in (PrimIDs.AMAX, PrimIDs.AMIN, PrimIDs.PROD, PrimIDs.VAR, PrimIDs.VAR_MEAN):
+    ex.register_supported(_pid, _reduce_check)
+
+
+def _is_leading_sum(b: BoundSymbol) -> bool:
+    return b.sym.id == PrimIDs.SUM and _sum_check(*b.args)
+
+
+def _needs_region_compiler(b: BoundSymbol) -> bool:
+    """Bound symbols the elementwise path (b200ex.pointwise + b200k_colsum) cannot express."""
+    return b.sym.id in _RC_PRIMS and not _is_leading_sum(b)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -772,6 +889,64 @@ _MACRO_IMPL: dict[Any, Callable] = {
 # --------------------------------------------------------------------------------------------------
 # Region lowering and launch (the role of FusionDefinitionWrapper, nvfuserex_impl.py:526-576)
 # --------------------------------------------------------------------------------------------------
+def _rc_nodes(b: BoundSymbol, r) -> list:
+    """Bound symbol -> region-compiler IR nodes.  `r` resolves a proxy to its (alias-resolved) value name."""
+    N = regionc.Node
+    sid = b.sym.id
+    out = b.output
+    if sid in _PW_OPNAME:
+        opname = _PW_OPNAME[sid]
+        dt, shape = _tdtype(out.dtype), tuple(out.shape)
+        if opname == "broadcast_in_dim":
+            a, _, bdims = b.args
+            return [N("broadcast_in_dim", out.name, dt, shape, (r(a),), {"bdims": tuple(bdims)})]
+        if opname == "convert":
+            return [N("convert", out.name, dt, shape, (r(b.args[0]),))]
+        return [N(opname, out.name, dt, shape, tuple(r(a) for a in b.args))]
+    kind = _RC_PRIMS[sid]
+    if kind in ("var", "var_mean"):
+        a, dims = b.args
+        corr = b.kwargs.get("correction", 0)
+        ashape = tuple(a.shape)
+        dims = tuple(sorted(d % len(ashape) for d in dims))
+        n = 1
+        for d in dims:
+            n *= ashape[d]
+        keep = tuple(d for d in range(len(ashape)) if d not in dims)
+        rshape = tuple(ashape[d] for d in keep)
+        var_out, mean_out = (out, None) if kind == "var" else (out[0], out[1])
+        f32, p = torch.float32, var_out.name
+        mean_name = mean_out.name if mean_out is not None else f"{p}__mean"
+        return [
+            N("reduce", f"{p}__s", f32, rshape, (r(a),), {"kind": "sum", "dims": dims}),
+            N("div", mean_name, f32, rshape, (f"{p}__s", float(n))),
+            N("broadcast_in_dim", f"{p}__mb", f32, ashape, (mean_name,), {"bdims": keep}),
+            N("sub", f"{p}__d", f32, ashape, (r(a), f"{p}__mb")),
+            N("mul", f"{p}__dd", f32, ashape, (f"{p}__d", f"{p}__d")),
+            N("reduce", f"{p}__ss", f32, rshape, (f"{p}__dd",), {"kind": "sum", "dims": dims}),
+            N("div", p, f32, rshape, (f"{p}__ss", float(max(0.0, n - corr)))),
+        ]
+    dt, shape = _tdtype(out.dtype), tuple(out.shape)
+    if kind in ("reshape", "squeeze"):
+        return [N("reshape", out.name, dt, shape, (r(b.args[0]),))]
+    if kind == "transpose":
+        return [N("transpose", out.name, dt, shape, (r(b.args[0]),), {"perm": tuple(b.args[1])})]
+    if kind == "slice":
+        a, starts, ends = b.args[:3]
+        strides = b.args[3] if len(b.args) > 3 else b.kwargs.get("strides")
+        return [N("slice", out.name, dt, shape, (r(a),), {"starts": tuple(starts), "strides": tuple(strides) if strides is not None else (1,) * len(starts)})]
+    if kind == "pad":
+        a, value, config = b.args
+        return [N("pad", out.name, dt, shape, (r(a),), {"value": value, "config": [tuple(c) for c in config]})]
+    if kind == "cat":
+        tensors, dim = b.args
+        return [N("cat", out.name, dt, shape, tuple(r(t) for t in tensors), {"dim": dim % len(shape)})]
+    if kind == "full":
+        return [N("full", out.name, dt, shape, (), {"value": b.args[1]})]
+    a, dims = b.args
+    return [N("reduce", out.name, dt, shape, (r(a),), {"kind": kind, "dims": tuple(dims)})]
+
+
 class _Step:
     """One launch (or one zero-copy alias) of a lowered region."""
 
@@ -800,6 +975,8 @@ class B200Region:
        canonical program is a known family runs that family's kernel); then the ready macro ops run.
     """
 
+    force_region_compiler = False  # tests: send purely elementwise components through b200ex.regionc as well
+
     def __init__(self, name: str, bsyms: list[BoundSymbol], inputs: list[Proxy], outputs: list[Proxy]):
         self.name = name
         self.bsyms = bsyms
@@ -807,7 +984,7 @@ class B200Region:
         self.output_names = [p.name for p in outputs]
         self.alias: dict[str, str] = {}
         self.steps = self._lower()
-        self.launch_kinds = [s.kind for s in self.steps]
+        self.launch_kinds = [s.kind for s in self.steps if s.kind != "view"]
 
     def __repr__(self):
         return f"B200Region({self.name}: {', '.join(self.launch_kinds)})"
@@ -857,6 +1034,14 @@ class B200Region:
                 consumers.setdefault(n, []).append(b)
         region_outs = {self._resolve(n) for n in self.output_names}
 
+        live, view_steps = self._peel_output_views(live, consumers, region_outs)
+        live, in_view_steps = self._peel_input_reshapes(live)
+        # A region with layout prims or general reductions goes through b200ex.regionc; then sums are ordinary nodes
+        # of its programs (fused column sums) instead of b200k_colsum steps.
+        self.use_rc = self.force_region_compiler or any(_needs_region_compiler(b) for b in live)
+        if self.use_rc and not jit.enabled():
+            raise PwUnsupported(f"{self.name}: layout / reduction prims need NVRTC (cuda-python), which is not importable here")
+
         absorbed: set[int] = set()
         macro_steps: dict[int, tuple] = {}  # id(bsym) -> (step, input names, output names)
         # uniform_philox tensors that only feed pointwise work of this region are not launched at all: they become
@@ -875,7 +1060,7 @@ class B200Region:
         for b in live:
             if id(b) in absorbed:
                 continue
-            if b.sym.id == PrimIDs.SUM:
+            if b.sym.id == PrimIDs.SUM and not self.use_rc:
                 macro_steps[id(b)] = self._colsum_step(b, prod, consumers, region_outs, absorbed)
                 continue
             if b.sym.id not in _MACRO_IMPL:
@@ -883,8 +1068,8 @@ class B200Region:
             fused = self._try_residual_fusion(b, prod, consumers, region_outs, absorbed)
             macro_steps[id(b)] = fused if fused is not None else self._macro_step(b)
 
-        steps: list[_Step] = []
-        available = set(self.input_names) | set(self.generated)
+        steps: list[_Step] = list(in_view_steps)
+        available = set(self.input_names) | set(self.generated) | self._input_views
         remaining = [b for b in live if id(b) not in absorbed]
         while remaining:
             progressed = False
@@ -919,7 +1104,76 @@ class B200Region:
                         progressed = True
             if not progressed:
                 raise PwUnsupported(f"{self.name}: cannot schedule region (cyclic or unknown dependency)")
-        return steps
+        return steps + view_steps
+
+    def _peel_input_reshapes(self, live: list[BoundSymbol]):
+        """`reshape` / `squeeze` applied directly to a region input (the [B*T, H] -> [B, T, H] of a GEMM result) is a
+        torch view taken before the first launch; the region then sees the reshaped tensor as its input."""
+        self._input_views: set[str] = set()
+        steps, rest = [], []
+        ins = set(self.input_names)
+        for b in live:
+            if b.sym.id in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE) and isinstance(b.args[0], TensorProxy) and self._resolve(b.args[0].name) in ins:
+                def run(env, src=self._resolve(b.args[0].name), out=b.output.name, shape=tuple(b.output.shape)):
+                    env[out] = env[src].reshape(shape)
+
+                steps.append(_Step("view", run))
+                self._input_views.add(b.output.name)
+            else:
+                rest.append(b)
+        return rest, steps
+
+    # ---- outputs that are views ------------------------------------------------------------------------------------
+    _VIEW_PRIMS = (PrimIDs.RESHAPE, PrimIDs.TRANSPOSE, PrimIDs.SLICE, PrimIDs.SQUEEZE, PrimIDs.BROADCAST_IN_DIM)
+
+    def _peel_output_views(self, live: list[BoundSymbol], consumers: dict, region_outs: set):
+        """Region outputs produced by reshape / transpose / slice / squeeze / expand of another value are not computed:
+        they are returned as torch views of that value, as the reference's torch executor returns them
+        (torchex.py:562-630) — e.g. the [B*T, H] and [H, B*T] GEMM operands that the dataflow partitioner glues onto
+        an RMSNorm backward.  No kernel, no bytes.  Peels chains from the outputs inwards; the view sources become
+        outputs of the remaining region."""
+        peeled: list[BoundSymbol] = []
+        ids: set[int] = set()
+        changed = True
+        while changed:
+            changed = False
+            for b in reversed(live):
+                if id(b) in ids or b.sym.id not in self._VIEW_PRIMS or not isinstance(b.args[0], TensorProxy):
+                    continue
+                name = b.output.name
+                if name not in region_outs or any(id(c) not in ids for c in consumers.get(name, [])):
+                    continue
+                ids.add(id(b))
+                peeled.append(b)
+                region_outs.add(self._resolve(b.args[0].name))  # the view's source is now what the region must produce
+                changed = True
+        if not peeled:
+            return live, []
+        steps = []
+        for b in reversed(peeled):  # sources before the views of views
+            src, out = self._resolve(b.args[0].name), b.output.name
+            region_outs.add(src)
+            sid = b.sym.id
+            if sid in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE):
+                fn = lambda t, shape=tuple(b.output.shape): t.reshape(shape)
+            elif sid == PrimIDs.TRANSPOSE:
+                fn = lambda t, perm=tuple(b.args[1]): t.permute(perm)
+            elif sid == PrimIDs.SLICE:
+                starts, ends = b.args[1], b.args[2]
+                strides = (b.args[3] if len(b.args) > 3 else b.kwargs.get("strides")) or [1] * len(starts)
+                fn = lambda t, idx=tuple(slice(a, e, st) for a, e, st in zip(starts, ends, strides)): t[idx]
+            else:
+                _, shape, bdims = b.args
+                view = [1] * len(shape)
+                for i, d in enumerate(bdims):
+                    view[d] = b.args[0].shape[i]
+                fn = lambda t, view=tuple(view), shape=tuple(shape): t.reshape(view).expand(shape)
+
+            def run(env, fn=fn, src=src, out=out):
+                env[out] = fn(env[src])
+
+            steps.append(_Step("view", run))
+        return [b for b in live if id(b) not in ids], steps
 
     def _macro_step(self, b: BoundSymbol):
         impl = _MACRO_IMPL[b.sym.id]
@@ -1110,11 +1364,39 @@ class B200Region:
             steps.extend(self._lower_component(comp, needed))
         return steps
 
+    def _lower_component_rc(self, comp: list[BoundSymbol], outs: list[str]) -> list[_Step]:
+        """A component with layout prims / reductions: translate to the region compiler's IR and let it cut the
+        component into generated kernels."""
+        produced = {o.name for b in comp for o in _outs_of(b)}
+        inputs: dict[str, tuple] = {}
+        nodes: list = []
+        r = lambda a: self._resolve(a.name) if isinstance(a, Proxy) else a
+        for b in comp:
+            for a in b.flat_proxy_args:
+                n = self._resolve(a.name)
+                if n not in produced and n not in inputs:
+                    if not isinstance(a, TensorProxy):
+                        raise PwUnsupported(f"{self.name}: non-tensor operand {n}")
+                    inputs[n] = (_tdtype(a.dtype), tuple(a.shape))
+            nodes.extend(_rc_nodes(b, r))
+        steps = []
+        for ln in regionc.compile_component(inputs, nodes, outs):
+            launch = regionc.RegionLaunch(ln)
+
+            def run(env, launch=launch):
+                env.update(launch.run(env))
+
+            step = _Step(launch.kind, run)
+            steps.append(step)
+        return steps
+
     def _lower_component(self, comp: list[BoundSymbol], needed: set) -> list[_Step]:
         produced = {o.name for b in comp for o in _outs_of(b)}
         outs = [o.name for b in comp for o in _outs_of(b) if o.name in needed]
         if not outs:
             return []
+        if self.use_rc and (self.force_region_compiler or any(b.sym.id in _RC_PRIMS for b in comp)):
+            return self._lower_component_rc(comp, outs)
         inputs: dict[str, tuple] = {}
         nodes: list[PwNode] = []
         r = lambda a: self._resolve(a.name) if isinstance(a, Proxy) else a
