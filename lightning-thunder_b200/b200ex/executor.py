@@ -789,11 +789,11 @@ def _rope_runtime_ok(qkv, cos, sin) -> bool:
 
 
 def _rope_fwd_impl(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem):
-    # Thunder keeps an executor-owned symbol even when its checker declined it (passes.py:78-81), so the
-    # callable has to cope with inputs outside the kernel's domain: those run the plain PyTorch definition.
-    if _rope_runtime_ok(qkv, cos, sin):
-        return ops.qkv_rope_fwd(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
-    return qkv_split_rope(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
+    # Thunder keeps an executor-owned symbol even when its checker declined it (passes.py:78-81).  There is no
+    # eager path inside the executor: inputs outside the kernel's domain are an error, not a silent torch run.
+    if not _rope_runtime_ok(qkv, cos, sin):
+        raise RuntimeError("b200_qkv_split_rope: inputs must be CUDA fp32/bf16/fp16 tensors of one dtype (no eager fallback inside the b200 executor)")
+    return ops.qkv_rope_fwd(qkv, cos, sin, n_head, n_query_groups, head_size, rope_n_elem)
 
 
 b200_qkv_split_rope = ex.register_operator("b200_qkv_split_rope", like=_qkv_split_rope_like, fn=_rope_fwd_impl, replaces=qkv_split_rope)
@@ -837,7 +837,9 @@ def _swiglu_runtime_ok(*ts) -> bool:
 
 
 def _swiglu_fwd_impl(a, b):
-    return ops.swiglu_fwd(a, b) if _swiglu_runtime_ok(a, b) else swiglu(a, b)
+    if not _swiglu_runtime_ok(a, b):
+        raise RuntimeError("b200_swiglu: inputs must be CUDA fp32/bf16/fp16 tensors of one shape and dtype (no eager fallback inside the b200 executor)")
+    return ops.swiglu_fwd(a, b)
 
 
 def _swiglu_bwd_meta(a, b, g):
@@ -1028,14 +1030,13 @@ class B200Region:
         prod: dict[str, BoundSymbol] = {o.name: b for b in self.bsyms for o in _outs_of(b)}
         dead = self._find_aliases(prod)
         live = [b for b in self.bsyms if id(b) not in dead]
+        region_outs = {self._resolve(n) for n in self.output_names}
+        live, view_steps = self._peel_output_views(live, region_outs)
+        live, in_view_steps = self._peel_input_reshapes(live)
         consumers: dict[str, list[BoundSymbol]] = {}
         for b in live:
             for n in self._arg_names(b):
                 consumers.setdefault(n, []).append(b)
-        region_outs = {self._resolve(n) for n in self.output_names}
-
-        live, view_steps = self._peel_output_views(live, consumers, region_outs)
-        live, in_view_steps = self._peel_input_reshapes(live)
         # A region with layout prims or general reductions goes through b200ex.regionc; then sums are ordinary nodes
         # of its programs (fused column sums) instead of b200k_colsum steps.
         self.use_rc = self.force_region_compiler or any(_needs_region_compiler(b) for b in live)
@@ -1126,54 +1127,76 @@ class B200Region:
     # ---- outputs that are views ------------------------------------------------------------------------------------
     _VIEW_PRIMS = (PrimIDs.RESHAPE, PrimIDs.TRANSPOSE, PrimIDs.SLICE, PrimIDs.SQUEEZE, PrimIDs.BROADCAST_IN_DIM)
 
-    def _peel_output_views(self, live: list[BoundSymbol], consumers: dict, region_outs: set):
-        """Region outputs produced by reshape / transpose / slice / squeeze / expand of another value are not computed:
-        they are returned as torch views of that value, as the reference's torch executor returns them
-        (torchex.py:562-630) — e.g. the [B*T, H] and [H, B*T] GEMM operands that the dataflow partitioner glues onto
-        an RMSNorm backward.  No kernel, no bytes.  Peels chains from the outputs inwards; the view sources become
-        outputs of the remaining region."""
-        peeled: list[BoundSymbol] = []
-        ids: set[int] = set()
-        changed = True
-        while changed:
-            changed = False
-            for b in reversed(live):
-                if id(b) in ids or b.sym.id not in self._VIEW_PRIMS or not isinstance(b.args[0], TensorProxy):
-                    continue
-                name = b.output.name
-                if name not in region_outs or any(id(c) not in ids for c in consumers.get(name, [])):
-                    continue
-                ids.add(id(b))
-                peeled.append(b)
-                region_outs.add(self._resolve(b.args[0].name))  # the view's source is now what the region must produce
-                changed = True
-        if not peeled:
-            return live, []
-        steps = []
-        for b in reversed(peeled):  # sources before the views of views
-            src, out = self._resolve(b.args[0].name), b.output.name
-            region_outs.add(src)
-            sid = b.sym.id
-            if sid in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE):
-                fn = lambda t, shape=tuple(b.output.shape): t.reshape(shape)
-            elif sid == PrimIDs.TRANSPOSE:
-                fn = lambda t, perm=tuple(b.args[1]): t.permute(perm)
-            elif sid == PrimIDs.SLICE:
-                starts, ends = b.args[1], b.args[2]
-                strides = (b.args[3] if len(b.args) > 3 else b.kwargs.get("strides")) or [1] * len(starts)
-                fn = lambda t, idx=tuple(slice(a, e, st) for a, e, st in zip(starts, ends, strides)): t[idx]
-            else:
-                _, shape, bdims = b.args
-                view = [1] * len(shape)
-                for i, d in enumerate(bdims):
-                    view[d] = b.args[0].shape[i]
-                fn = lambda t, view=tuple(view), shape=tuple(shape): t.reshape(view).expand(shape)
+    def _peel_output_views(self, live: list[BoundSymbol], region_outs: set):
+        """Region outputs that are views of a materialised value are not computed: they are returned as torch views
+        of it, as the reference's torch executor returns them (torchex.py:562-630) — e.g. the [B*T, H] and [H, B*T]
+        GEMM operands that the dataflow partitioner glues onto an RMSNorm backward.  No kernel, no bytes.
 
-            def run(env, fn=fn, src=src, out=out):
-                env[out] = fn(env[src])
+        A chain qualifies when, read from its source outwards, it is reshapes / squeezes of a dense value followed by
+        transposes / slices / expands (always views in torch); a reshape on top of one of those could copy, so it —
+        and everything beneath it — stays inside the kernel as an index map.  The source must be a region input or a
+        value some kernel of the region writes anyway."""
+        prod = {o.name: b for b in live for o in _outs_of(b)}
+        ins = set(self.input_names)
+        steps, peeled_outs = [], set()
+        for out in sorted(region_outs):
+            chain, name = [], out
+            while name in prod and prod[name].sym.id in self._VIEW_PRIMS and isinstance(prod[name].args[0], TensorProxy):
+                chain.append(prod[name])
+                name = self._resolve(prod[name].args[0].name)
+            if not chain or (name not in ins and name not in prod):
+                continue
+            # inner to outer: R* V*
+            seen_v, ok = False, True
+            for b in reversed(chain):
+                is_r = b.sym.id in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE)
+                if is_r and seen_v and b.sym.id == PrimIDs.RESHAPE:
+                    ok = False
+                    break
+                seen_v = seen_v or not is_r
+            if not ok:
+                continue
+            fns = []
+            for b in reversed(chain):
+                sid = b.sym.id
+                if sid in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE):
+                    fns.append(lambda t, shape=tuple(b.output.shape): t.reshape(shape))
+                elif sid == PrimIDs.TRANSPOSE:
+                    fns.append(lambda t, perm=tuple(b.args[1]): t.permute(perm))
+                elif sid == PrimIDs.SLICE:
+                    starts, ends = b.args[1], b.args[2]
+                    strides = (b.args[3] if len(b.args) > 3 else b.kwargs.get("strides")) or [1] * len(starts)
+                    fns.append(lambda t, idx=tuple(slice(a, e, st) for a, e, st in zip(starts, ends, strides)): t[idx])
+                else:
+                    _, shape, bdims = b.args
+                    view = [1] * len(shape)
+                    for k, d in enumerate(bdims):
+                        view[d] = b.args[0].shape[k]
+                    fns.append(lambda t, view=tuple(view), shape=tuple(shape): t.reshape(view).expand(shape))
+
+            def run(env, fns=tuple(fns), src=name, out=out):
+                t = env[src]
+                for f in fns:
+                    t = f(t)
+                env[out] = t
 
             steps.append(_Step("view", run))
-        return [b for b in live if id(b) not in ids], steps
+            peeled_outs.add(out)
+            if name not in ins:
+                region_outs.add(name)
+        if not steps:
+            return live, []
+        region_outs -= peeled_outs
+        # bound symbols that only fed the peeled views are dead now
+        need = set(region_outs)
+        keep = []
+        for b in reversed(live):
+            if b.sym.id in self._VIEW_PRIMS or b.sym.id in _PW_OPNAME or b.sym.id in _RC_PRIMS:
+                if not any(o.name in need for o in _outs_of(b)):
+                    continue
+            keep.append(b)
+            need.update(self._arg_names(b))
+        return keep[::-1], steps
 
     def _macro_step(self, b: BoundSymbol):
         impl = _MACRO_IMPL[b.sym.id]

@@ -130,6 +130,7 @@ class Program:
     phase: list | None = None  # row kernels: phase of every ssa value
     full: list | None = None  # row kernels: does the value vary inside a row?
     in_shapes: dict | None = None  # input name -> shape, for the inputs the leaves read
+    order: list | None = None  # flat kernels: variables from fastest to slowest in the thread mapping
 
     @property
     def row_len(self):
@@ -247,7 +248,17 @@ class _Builder:
             return True
         if rhi < lo or rlo >= hi:
             return False
-        key = (a[0], max(lo, rlo) - a[1], min(hi, rhi + 1) - a[1])
+        terms, clo, chi = a[0], max(lo, rlo) - a[1], min(hi, rhi + 1) - a[1]
+        # lo <= g*rest + k*v < hi with lo, hi multiples of g and 0 <= k*v < g does not depend on v: drop the term and
+        # divide by g (a `cat` boundary at a multiple of the low digit's span only tests the high digits)
+        while len(terms) > 1:
+            v, k = min(terms, key=lambda t: abs(t[1]))
+            g = math.gcd(*[c for u, c in terms if u != v], clo, chi)
+            if k <= 0 or g <= k * (self.ext[v] - 1):
+                break
+            terms = tuple((u, c // g) for u, c in terms if u != v)
+            clo, chi = clo // g, chi // g
+        key = (terms, clo, chi)
         if key not in self.cond_ids:
             self.cond_ids[key] = len(self.conds)
             self.conds.append(key)
@@ -580,7 +591,17 @@ def _build(kind, shape, n_outer_dims, inputs, producer, meta, outs_spec):
                     sid = B.value(n.args[0], coords)
                 outputs.append(Out(name, dt, tuple(oshape), sid, okind))
             P = Program(kind, B.ext, B.n_outer, B.leaves, B.conds, B.ssa, outputs, phase=B.phase, full=B.full)
+            if kind == "flat" and B.ext:
+                # conditions on the innermost variable whose boundaries share a granule G: split it into (hi, lo) so
+                # that they test `hi` only and the thread mapping can keep a warp on one side of every boundary
+                vd = len(B.ext) - 1
+                bounds = [b for terms, lo, hi in B.conds if terms == ((vd, 1),) for b in (lo, hi)]
+                if bounds and not any(vd in dict(terms) and terms != ((vd, 1),) for terms, _, _ in B.conds):
+                    G = math.gcd(B.ext[vd], *bounds)
+                    if 8 <= G < B.ext[vd] and G % 8 == 0:
+                        raise _SplitVar(vd, G)
             P.W = _choose_width(P, inputs)
+            P.order = _thread_order(P)
             P.in_shapes = {lf.name: tuple(inputs[lf.name][1]) for lf in P.leaves}
             P.signature = _sig(P, P.in_shapes)
             return P
@@ -592,6 +613,41 @@ def _build(kind, shape, n_outer_dims, inputs, producer, meta, outs_spec):
             dims = [list(x) for x in dims]
             dims[d][i:i + 1] = [n // s.inner, s.inner]
     raise PwUnsupported("reshape: variable splitting did not converge")
+
+
+def _thread_order(P: Program) -> list:
+    """Flat kernels: how the linear work-item index maps to the iteration variables, fastest first, as
+    (variable, part, size) with part "all" | "lo" | "hi".  Without conditions: the natural order.  With conditions a
+    CTA's worth of items (innermost chunks x a block of the next unconditioned variables) comes first, then the
+    conditioned variables, then the rest: a warp never straddles a `cat` / `pad` boundary (no divergence), and the
+    two sides of a boundary are still visited close together in time (the partner halves of a rotary pair hit L2)."""
+    nv = len(P.ext)
+    if not nv:
+        return []
+    cond_vars = {v for terms, _, _ in P.conds for v, _ in terms}
+    if not cond_vars:
+        return [(v, "all", P.ext[v]) for v in range(nv - 1, -1, -1)]
+    order = [(nv - 1, "all", P.ext[nv - 1])]
+    have = max(1, P.ext[nv - 1] // max(P.W, 1))
+    free = [v for v in range(nv - 2, -1, -1) if v not in cond_vars]
+    tail = []
+    while free and have < 256:
+        v = free.pop(0)
+        n = P.ext[v]
+        if have * n <= 256:
+            order.append((v, "all", n))
+            have *= n
+            continue
+        b = next(d for d in range(1, n + 1) if n % d == 0 and have * d >= 256)
+        if b == n:
+            order.append((v, "all", n))
+        else:
+            order.append((v, "lo", b))
+            tail.append((v, "hi", n // b))
+        have *= b
+    order += [(v, "all", P.ext[v]) for v in range(nv - 2, -1, -1) if v in cond_vars]
+    order += tail + [(v, "all", P.ext[v]) for v in free]
+    return order
 
 
 def _choose_width(P: Program, inputs) -> int:
@@ -663,8 +719,10 @@ def compile_component(inputs: dict, nodes: list, outputs: list) -> list:
         while n is not None and n.op == "reshape" and n.args[0] in producer:
             src = n.args[0]
             n = producer[src]
-        if src != o:
+        if src != o and src in outputs:  # free only when the source is written anyway
             views[o] = (src, tuple(meta[o][1]))
+        else:
+            src = o
         if src not in want:
             want.append(src)
 
@@ -698,7 +756,7 @@ def compile_component(inputs: dict, nodes: list, outputs: list) -> list:
             shape = tuple(meta[a][1])
             n_outer = len(producer[cols[0]].attrs["dims"])
         outer, red = shape[:n_outer], shape[n_outer:]
-        spec = []
+        spec, flat_outs = [], []
         for o in need1:
             oshape = tuple(meta[o][1])
             if o in cols:
@@ -710,12 +768,14 @@ def compile_component(inputs: dict, nodes: list, outputs: list) -> list:
             elif tuple(s for s in oshape if s != 1) == tuple(s for s in outer if s != 1) and math.prod(red) > 1:
                 spec.append((o, "row"))
             else:
-                raise PwUnsupported(f"output {o} of shape {oshape} does not fit the row structure {outer} | {red}")
+                flat_outs.append(o)  # e.g. an upcast weight saved for the backward: its own small elementwise kernel
         if spec:
             launches.append(Launch(_build("row", shape, n_outer, inputs, producer, meta, spec), {}))
     else:
+        flat_outs = need1
+    if flat_outs:
         groups: dict = {}
-        for o in need1:
+        for o in flat_outs:
             groups.setdefault(tuple(meta[o][1]), []).append(o)
         for shape, outs in groups.items():
             for i in range(0, len(outs), MAX_OUTS):
@@ -835,11 +895,8 @@ def leaf_modes(P: Program, leaf_tensors) -> tuple:
         if dt is None:
             raise RuntimeError(f"b200ex region: operand {lf.name} has unsupported dtype {t.dtype}")
         ks = [dict(c[0]).get(vd, 0) for c in lf.coords]
-        if not any(ks):
-            modes.append(("b", dt))
-            continue
-        if W == 1:
-            modes.append(("s", dt))
+        if not any(ks) or W == 1:
+            modes.append(("b" if not any(ks) else "s", dt))
             continue
         last = len(ks) - 1
         c = lf.coords[last]
@@ -849,7 +906,12 @@ def leaf_modes(P: Program, leaf_tensors) -> tuple:
             align = min(16, W * esz)
             ok = t.data_ptr() % align == 0 and all((t.stride(i) * esz) % align == 0 for i in range(last) if t.shape[i] != 1)
         modes.append(("v" if ok else "s", dt))
-    return tuple(modes)
+    # strides are compiled into the kernel (shapes already are): index arithmetic folds to a few 32-bit operations
+    out = []
+    for (m, dt), lf, t in zip(modes, P.leaves, leaf_tensors):
+        st = tuple(0 if t.shape[i] == 1 else int(t.stride(i)) for i in range(len(lf.coords)))
+        out.append((m, dt, st))
+    return tuple(out)
 
 
 def _aff_c(a, names, cast="") -> str:
@@ -879,19 +941,23 @@ class _Gen:
             lin = f"({lin} + {dict(terms)[self.vd]} * {e})"
         return f"({lin} >= {lo} && {lin} < {hi})"
 
-    def leaf_offset(self, k, names):
-        lf = self.P.leaves[k]
-        terms = []
+    def leaf_aff(self, k):
+        """Element offset of leaf k as one affine form over the iteration variables (strides are compile-time)."""
+        lf, st = self.P.leaves[k], self.modes[k][2]
+        a = _ZERO
         for i, c in enumerate(lf.coords):
-            if not c[0] and not c[1]:
-                continue
-            terms.append(f"(i64){_aff_c(c, names)} * P.in[{self.slot[k]}].st[{i}]")
-        return " + ".join(terms) if terms else "0"
+            a = _aff_add(a, _aff_scale(c, st[i]))
+        return a
+
+    def leaf_offset(self, k, names):
+        a = self.leaf_aff(k)
+        span = abs(a[1]) + sum(abs(c) * (self.P.ext[v] - 1) for v, c in a[0])
+        if span < 2**31:
+            return f"(i64){_aff_c(a, names)}"
+        return _aff_c(a, [f"(i64){n}" for n in names])
 
     def leaf_estride(self, k):
-        lf = self.P.leaves[k]
-        terms = [f"{dict(c[0])[self.vd]} * P.in[{self.slot[k]}].st[{i}]" for i, c in enumerate(lf.coords) if dict(c[0]).get(self.vd, 0)]
-        return " + ".join(terms) if terms else "0"
+        return str(dict(self.leaf_aff(k)[0]).get(self.vd, 0))
 
     def ssa_line(self, i, ref, leafref, predref):
         op, a, b, c, imm = self.P.ssa[i]
@@ -920,6 +986,35 @@ def _fold(P: Program, assume: dict):
     outputs; undecided = conditions the live part still depends on."""
     ONE, ZERO = _f32_bits(1.0), _f32_bits(0.0)
     res: list = []
+    # conditions on the same linear form are ranges of one quantity: what is decided narrows that quantity's range,
+    # which decides others (after "not [0, 64)" on a 128-wide dim, "[64, 128)" is known to hold)
+    assume = dict(assume)
+    by_terms: dict = {}
+    for ci, (terms, lo, hi) in enumerate(P.conds):
+        by_terms.setdefault(terms, []).append(ci)
+    for terms, cis in by_terms.items():
+        lo = sum(k * (P.ext[v] - 1) for v, k in terms if k < 0)
+        hi = sum(k * (P.ext[v] - 1) for v, k in terms if k > 0)
+        changed = True
+        while changed:
+            changed = False
+            for ci in cis:
+                if ci not in assume:
+                    continue
+                clo, chi = P.conds[ci][1], P.conds[ci][2]
+                if assume[ci]:
+                    nlo, nhi = max(lo, clo), min(hi, chi - 1)
+                else:
+                    nlo, nhi = (chi if clo <= lo < chi else lo), (clo - 1 if clo <= hi < chi else hi)
+                if (nlo, nhi) != (lo, hi):
+                    lo, hi, changed = nlo, nhi, True
+        for ci in cis:
+            if ci not in assume:
+                clo, chi = P.conds[ci][1], P.conds[ci][2]
+                if lo >= clo and hi < chi:
+                    assume[ci] = True
+                elif hi < clo or lo >= chi:
+                    assume[ci] = False
 
     def R(x):
         return res[x] if x >= 0 else None
@@ -989,23 +1084,28 @@ def generate_flat(P: Program, modes: tuple, unroll: int) -> str:
     L.append("    #pragma unroll")
     L.append(f"    for (int u = 0; u < {U}; ++u) {{")
     L.append(f"      {it} r = base + ({it})u * 256; live[u] = r < TOTAL; if (!live[u]) r = 0;")
-    for k in range(nv - 1, -1, -1):
-        e = ext[k] // W if k == nv - 1 else ext[k]
+    order = P.order if P.order is not None else [(k, "all", ext[k]) for k in range(nv - 1, -1, -1)]
+    lo_size = {k: n for k, part, n in order if part == "lo"}
+    for pos, (k, part, n) in enumerate(order):  # fastest first
+        e = n // W if k == nv - 1 else n
         mul = f" * {W}" if (k == nv - 1 and W > 1) else ""
-        if k == 0:
-            L.append(f"      x[u][0] = r{mul};")
+        val = "r" if pos == len(order) - 1 else f"(r % {e})"
+        step = "" if pos == len(order) - 1 else f" r /= {e};"
+        if part == "hi":
+            L.append(f"      x[u][{k}] += {val} * {lo_size[k]};{step}")
         else:
-            L.append(f"      x[u][{k}] = (r % {e}){mul}; r /= {e};")
+            L.append(f"      x[u][{k}] = {val}{mul};{step}")
     inames = [f"(int)x[u][{k}]" for k in range(nv)] if it == "u32" else [f"x[u][{k}]" for k in range(nv)]
     for ci in range(len(P.conds)):
         L.append(f"      cn[u][{ci}] = {G.cond_expr(ci, inames)};")
     L.append("    }")
     # linear offset of the item in every (fresh, contiguous) output
     lin, stride = [], 1
+    cast = "" if math.prod(ext) < 2**31 else "(i64)"
     for k in range(nv - 1, -1, -1):
-        lin.append(f"(i64)x[u][{k}] * {stride}" if stride != 1 else f"(i64)x[u][{k}]")
+        lin.append(f"{cast}x[u][{k}] * {stride}u" if stride != 1 else f"{cast}x[u][{k}]")
         stride *= ext[k]
-    out_off = " + ".join(lin) if lin else "0"
+    out_off = "(i64)(" + (" + ".join(lin) if lin else "0") + ")"
 
     def load(k, ind, dst):
         lf = P.leaves[k]

@@ -7,6 +7,8 @@
 // and the valid-target count.
 // Backward: one pass, reads logits, writes dlogits; log p is recomputed from the saved max and
 // log-sum and rounded to the storage dtype exactly where the reference holds it as a tensor.
+#include <cstdio>
+
 #include "common.cuh"
 
 namespace b200k {
@@ -110,7 +112,13 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
                 row_logsum[row] = logsum;
                 const int64_t tg = target[row];
                 float nll = 0.f;
-                if (tg != ignore_index && tg >= 0 && tg < vocab) {
+                if (tg != ignore_index && (tg < 0 || tg >= vocab)) {
+                    // ATen's nll_loss device-asserts on a class index outside [0, vocab) (the reference's oracle path,
+                    // torchex.py:1731-1783); same contract here: report and trap, never score the row as 0.
+                    printf("b200k_cross_entropy_fwd: target %lld of row %lld is outside [0, %lld)\n", (long long)tg, (long long)row, (long long)vocab);
+                    __trap();
+                }
+                if (tg != ignore_index) {
                     // -log p of the target, rounded through the storage dtype like the reference's log_softmax output
                     nll = -V::rnd((V::load1(x, tg) - t.m) - logsum);
                 }
@@ -181,6 +189,10 @@ ce_bwd_kernel(const T* __restrict__ g, const T* __restrict__ logits, const int64
         T* dx = dlogits + row * vocab;
         const int64_t tg = target[row];
         const bool valid = tg != ignore_index;
+        if (valid && (tg < 0 || tg >= vocab)) {
+            if (tid == 0) printf("b200k_cross_entropy_bwd: target %lld of row %lld is outside [0, %lld)\n", (long long)tg, (long long)row, (long long)vocab);
+            __trap();
+        }
         const float d = valid ? d_all : 0.f;
         const float m = row_max[row], ls = row_logsum[row];
         if (!valid) {
