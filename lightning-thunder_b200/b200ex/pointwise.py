@@ -567,6 +567,13 @@ class PwLaunch:
                 raise RuntimeError(f"b200ex pointwise: operand {name} is not a CUDA tensor")
             if t.dim() != len(mapping):
                 raise RuntimeError(f"b200ex pointwise: operand {name} has rank {t.dim()}, expected {len(mapping)}")
+            if t.dtype not in DTYPE_CODE:
+                # The reference's traces are not always dtype-consistent: the backward of `amax` hands an int64 tie
+                # count to a proxy declared bool.  Integers enter the program as the fp32 values they are.
+                if t.dtype in (torch.int64, torch.int32, torch.int16, torch.int8, torch.uint8):
+                    t = t.to(torch.float32)
+                else:
+                    raise RuntimeError(f"b200ex pointwise: operand {name} has unsupported dtype {t.dtype}")
             tensors.append(t)
             dev = dev or t.device
         if dev is None:

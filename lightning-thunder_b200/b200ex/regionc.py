@@ -31,6 +31,7 @@ from __future__ import annotations
 import ctypes
 import hashlib
 import math
+import os
 import threading
 from dataclasses import dataclass, field
 
@@ -1204,6 +1205,11 @@ def row_geometry(P: Program):
 
 
 def generate_row(P: Program, modes: tuple) -> str:
+    """Row-persistent kernel.  One row lives in the registers of T threads (a warp, or a whole CTA), C interleaved
+    chunks of W elements per thread.  16-bit operands stay packed (one 16-byte register quad per chunk) and are
+    unpacked where they are used, which halves their register cost and pays for a second buffer: the next row's loads
+    are issued before the current row's reductions, so the barriers and shuffles of one row overlap the memory
+    latency of the next.  Values on the far side of a reduction are recomputed from the resident operands."""
     G = _Gen(P, modes)
     in_names, G.slot = input_slots(P)
     W, ext, nv, no = P.W, P.ext, len(P.ext), P.n_outer
@@ -1214,38 +1220,60 @@ def generate_row(P: Program, modes: tuple) -> str:
     reduces = [i for i, s in enumerate(P.ssa) if s[0].startswith("reduce_")]
     leaf_sid = _leaf_sids(P)
     n_inner = nv - no
-    names_c = [f"xo[{k}]" for k in range(no)] + [f"xi[c][{k - no}]" for k in range(no, nv)]
-    names_r = [f"xo[{k}]" for k in range(no)] + ["0"] * n_inner
-    # conditions by what they depend on: the row only (scalar per row), the position in the row only (computed once
-    # per thread), or both (recomputed per row)
     cond_cls = []
     for terms, _, _ in P.conds:
         o, i = any(v < no for v, _ in terms), any(v >= no for v, _ in terms)
         cond_cls.append("mixed" if (o and i) else ("inner" if i else "outer"))
-    cref = lambda ci: {"outer": f"cr{ci}", "inner": f"ci_[c][{ci}]", "mixed": f"cm_[c][{ci}]"}[cond_cls[ci]]
 
     def uses_outer(lf):
         vs = {v for c in lf.coords for v, _ in c[0]} | {v for ci in lf.guard for v, _ in P.conds[ci][0]}
         return any(v < no for v in vs)
 
-    def load_full_leaf(k, indent):
+    full_leaves = [k for k in range(len(P.leaves)) if P.full[leaf_sid[k]]]
+    hoisted = [k for k in full_leaves if not uses_outer(P.leaves[k])]
+    per_row = [k for k in full_leaves if k not in hoisted]
+    scalars = [k for k in range(len(P.leaves)) if k not in full_leaves]
+    packed = {k for k in per_row if modes[k][0] == "v" and modes[k][1] in ("bf16", "f16") and W == 8}
+    cost = sum(C * (4 if k in packed else W) for k in per_row)
+    fixed = (len(hoisted) + len(cols)) * C * W
+    nbuf = 2 if (per_row and 2 * cost + fixed <= 150 and os.environ.get("B200EX_ROW_PREFETCH", "1") != "0") else 1
+
+    names_i = lambda b: [f"xo{b}[{k}]" for k in range(no)] + [f"xi[c][{k - no}]" for k in range(no, nv)]
+    names_r = lambda b: [f"xo{b}[{k}]" for k in range(no)] + ["0"] * n_inner
+
+    def cref(ci, b):
+        return {"outer": f"cr{b}_{ci}", "inner": f"ci_[c][{ci}]", "mixed": f"cm{b}_[c][{ci}]"}[cond_cls[ci]]
+
+    def load_full(k, b, ind, dst):
         lf = P.leaves[k]
         dt, ptr = modes[k][1], f"P.in[{G.slot[k]}].ptr"
-        out = [f"{indent}#pragma unroll", f"{indent}for (int c = 0; c < C_; ++c) {{"]
-        g = " && ".join(["lc[c]"] + [cref(ci) for ci in lf.guard])
-        off = G.leaf_offset(k, names_c)
-        if modes[k][0] == "v":
-            out.append(f"{indent}  if ({g}) ldv_{dt}<W_>({ptr}, {off}, v{k}[c]); else {{ for (int e = 0; e < W_; ++e) v{k}[c][e] = 0.f; }}")
+        g = " && ".join(["lc[c]"] + [cref(ci, b) for ci in lf.guard])
+        off = G.leaf_offset(k, names_i(b))
+        out = [f"{ind}#pragma unroll", f"{ind}for (int c = 0; c < C_; ++c) {{"]
+        if k in packed:
+            out.append(f"{ind}  {dst}[c] = ({g}) ? ldg16((const u16*){ptr} + {off}) : V4{{0u, 0u, 0u, 0u}};")
+        elif modes[k][0] == "v":
+            out.append(f"{ind}  if ({g}) ldv_{dt}<W_>({ptr}, {off}, {dst}[c]); else {{ for (int e = 0; e < W_; ++e) {dst}[c][e] = 0.f; }}")
         elif modes[k][0] == "b":
-            out.append(f"{indent}  {{ const float b = ({g}) ? ld1_{dt}({ptr}, {off}) : 0.f; for (int e = 0; e < W_; ++e) v{k}[c][e] = b; }}")
+            out.append(f"{ind}  {{ const float b_ = ({g}) ? ld1_{dt}({ptr}, {off}) : 0.f; for (int e = 0; e < W_; ++e) {dst}[c][e] = b_; }}")
         else:
-            out.append(f"{indent}  if ({g}) {{ const i64 o = {off}, es = {G.leaf_estride(k)}; for (int e = 0; e < W_; ++e) v{k}[c][e] = ld1_{dt}({ptr}, o + e * es); }} else {{ for (int e = 0; e < W_; ++e) v{k}[c][e] = 0.f; }}")
-        out.append(f"{indent}}}")
+            out.append(f"{ind}  if ({g}) {{ const i64 o = {off}, es = {G.leaf_estride(k)}; for (int e = 0; e < W_; ++e) {dst}[c][e] = ld1_{dt}({ptr}, o + e * es); }} else {{ for (int e = 0; e < W_; ++e) {dst}[c][e] = 0.f; }}")
+        out.append(f"{ind}}}")
         return out
 
+    def leaf_ref(k, b):
+        if k in hoisted:
+            return f"vh{k}[c][e]"
+        if k in packed:
+            return f"unp_{modes[k][1]}(z{k}, e)"
+        return f"v{b}_{k}[c][e]"
+
     L = [G.head(len(in_names))]
+    L.append("__device__ __forceinline__ float unp_bf16(const V4& v, int e) { const u32 w = (e >> 1) == 0 ? v.x : ((e >> 1) == 1 ? v.y : ((e >> 1) == 2 ? v.z : v.w)); return (e & 1) ? __uint_as_float(w & 0xffff0000u) : __uint_as_float(w << 16); }")
+    L.append("__device__ __forceinline__ float unp_f16(const V4& v, int e) { const u32 w = (e >> 1) == 0 ? v.x : ((e >> 1) == 1 ? v.y : ((e >> 1) == 2 ? v.z : v.w)); return (e & 1) ? h2f(w >> 16) : h2f(w & 0xffffu); }")
     L.append(f"#define T_ {T}\n#define C_ {C}\n#define W_ {W}\n#define R_ {R}")
-    L.append(f'extern "C" __global__ void __launch_bounds__({block}) rk_main(const __grid_constant__ Params P) {{')
+    # at most 128 registers per thread: two 256-thread CTAs (or four 128-thread ones) stay resident per SM
+    L.append(f'extern "C" __global__ void __launch_bounds__({block}, {max(1, 512 // block)}) rk_main(const __grid_constant__ Params P) {{')
     if T > 32:
         L.append(f"  __shared__ float red_s[{max(len(reduces), 1)}][{T // 32}];")
     L.append("  const int tr = threadIdx.x % T_, rslot = threadIdx.x / T_;")
@@ -1266,45 +1294,52 @@ def generate_row(P: Program, modes: tuple) -> str:
             L.append(f"    xi[c][{k - no}] = r % {ext[k]}; r /= {ext[k]};")
     for ci, cls in enumerate(cond_cls):
         if cls == "inner":
-            L.append(f"    ci_[c][{ci}] = {G.cond_expr(ci, names_c)};")
+            L.append(f"    ci_[c][{ci}] = {G.cond_expr(ci, names_i(0))};")
     L.append("  }")
     # operands that do not depend on the row (weights, biases) are loaded once per thread
-    hoisted = [k for k, lf in enumerate(P.leaves) if P.full[leaf_sid[k]] and not uses_outer(lf)]
     for k in hoisted:
-        L.append(f"  float v{k}[C_][W_];")
-        L += load_full_leaf(k, "  ")
-    L.append(f"  for (i64 row = (i64)blockIdx.x * {RPC} + rslot; row < {NR}; row += (i64)gridDim.x * {RPC}) {{")
-    L.append(f"    int xo[{max(no, 1)}]; {{ i64 r = row;")
-    for k in range(no - 1, -1, -1):
-        if k == 0:
-            L.append("      xo[0] = (int)r;")
-        else:
-            L.append(f"      xo[{k}] = (int)(r % {ext[k]}); r /= {ext[k]};")
-    L.append("    }")
-    for ci, cls in enumerate(cond_cls):
-        if cls == "outer":
-            L.append(f"    const bool cr{ci} = {G.cond_expr(ci, names_r)};")
-    if "mixed" in cond_cls:
-        L.append(f"    bool cm_[C_][{len(P.conds)}];")
-        L.append("    #pragma unroll")
-        L.append("    for (int c = 0; c < C_; ++c) {")
+        L.append(f"  float vh{k}[C_][W_];")
+        was, packed_k = modes[k], k in packed
+        L += load_full(k, 0, "  ", f"vh{k}")
+    # per-buffer state of a row: coordinates, conditions, operands
+    for b in range(nbuf):
+        L.append(f"  int xo{b}[{max(no, 1)}];")
         for ci, cls in enumerate(cond_cls):
-            if cls == "mixed":
-                L.append(f"      cm_[c][{ci}] = {G.cond_expr(ci, names_c)};")
-        L.append("    }")
-    for k, lf in enumerate(P.leaves):
-        if k in hoisted:
-            continue
-        dt, ptr = modes[k][1], f"P.in[{G.slot[k]}].ptr"
-        if not P.full[leaf_sid[k]]:
-            g = " && ".join([f"cr{ci}" for ci in lf.guard]) or "true"
-            L.append(f"    const float s{k} = ({g}) ? ld1_{dt}({ptr}, {G.leaf_offset(k, names_r)}) : 0.f;")
-        else:
-            L.append(f"    float v{k}[C_][W_];")
-            L += load_full_leaf(k, "    ")
+            if cls == "outer":
+                L.append(f"  bool cr{b}_{ci} = false;")
+        if "mixed" in cond_cls:
+            L.append(f"  bool cm{b}_[C_][{len(P.conds)}];")
+        for k in per_row:
+            L.append(f"  V4 w{b}_{k}[C_];" if k in packed else f"  float v{b}_{k}[C_][W_];")
+        for k in scalars:
+            L.append(f"  float s{b}_{k} = 0.f;")
+
+    def emit_load(b, rowvar, ind):
+        L.append(f"{ind}{{ i64 r = {rowvar};")
+        for k in range(no - 1, -1, -1):
+            if k == 0:
+                L.append(f"{ind}  xo{b}[0] = (int)r;")
+            else:
+                L.append(f"{ind}  xo{b}[{k}] = (int)(r % {ext[k]}); r /= {ext[k]};")
+        L.append(f"{ind}}}")
+        for ci, cls in enumerate(cond_cls):
+            if cls == "outer":
+                L.append(f"{ind}cr{b}_{ci} = {G.cond_expr(ci, names_r(b))};")
+        if "mixed" in cond_cls:
+            L.append(f"{ind}#pragma unroll")
+            L.append(f"{ind}for (int c = 0; c < C_; ++c) {{")
+            for ci, cls in enumerate(cond_cls):
+                if cls == "mixed":
+                    L.append(f"{ind}  cm{b}_[c][{ci}] = {G.cond_expr(ci, names_i(b))};")
+            L.append(f"{ind}}}")
+        for k in scalars:
+            lf = P.leaves[k]
+            g = " && ".join([f"cr{b}_{ci}" for ci in lf.guard]) or "true"
+            L.append(f"{ind}s{b}_{k} = ({g}) ? ld1_{modes[k][1]}(P.in[{G.slot[k]}].ptr, {G.leaf_offset(k, names_r(b))}) : 0.f;")
+        for k in per_row:
+            L.extend(load_full(k, b, ind, f"w{b}_{k}" if k in packed else f"v{b}_{k}"))
 
     def needed_for(targets):
-        """Values that vary inside the row and must be evaluated in the element loop to produce `targets`."""
         need, stack = set(), list(targets)
         while stack:
             i = stack.pop()
@@ -1314,88 +1349,121 @@ def generate_row(P: Program, modes: tuple) -> str:
             stack.extend(x for x in P.ssa[i][1:4] if x >= 0)
         return sorted(need)
 
-    emitted_row = set()
+    def emit_body(b, rowvar, ind):
+        L.append(f"{ind}{{")
+        ind2 = ind + "  "
+        emitted_row = set()
 
-    def emit_row_scalars(upto_phase):
-        for i, s in enumerate(P.ssa):
-            if P.full[i] or i in emitted_row or P.phase[i] > upto_phase or s[0].startswith("reduce_"):
-                continue
-            expr = G.ssa_line(i, lambda a: f"q{a}", lambda k: f"s{k}", lambda ci: f"(cr{ci} ? 1.f : 0.f)")
-            L.append(f"    const float q{i} = {expr};")
-            emitted_row.add(i)
+        def emit_row_scalars(upto_phase):
+            for i, s_ in enumerate(P.ssa):
+                if P.full[i] or i in emitted_row or P.phase[i] > upto_phase or s_[0].startswith("reduce_"):
+                    continue
+                expr = G.ssa_line(i, lambda a: f"q{a}", lambda k: f"s{b}_{k}", lambda ci: f"(cr{b}_{ci} ? 1.f : 0.f)")
+                L.append(f"{ind2}const float q{i} = {expr};")
+                emitted_row.add(i)
 
-    ref = lambda a: f"t{a}" if P.full[a] else f"q{a}"
-    for ph in range(nph):
-        emit_row_scalars(ph)
-        last = ph == nph - 1
-        reds = [i for i in reduces if P.phase[P.ssa[i][1]] == ph]
-        targets = [P.ssa[i][1] for i in reds]
-        out_full = [(k, o) for k, o in enumerate(P.outputs) if o.kind in ("full", "col")] if last else []
-        targets += [o.sid for _, o in out_full]
-        need = needed_for(targets)
-        for i in reds:
-            L.append(f"    float p{i} = {_RED_ID[P.ssa[i][0][7:]]};")
-        if need or out_full:
-            L.append("    #pragma unroll")
-            L.append("    for (int c = 0; c < C_; ++c) if (lc[c]) {")
-            for k, o in out_full:
-                if o.kind == "full":
-                    L.append(f"      float o{k}[W_];")
-            L.append("      #pragma unroll")
-            L.append("      for (int e = 0; e < W_; ++e) {")
-            for i in need:
-                expr = G.ssa_line(i, ref, lambda k: f"v{k}[c][e]", lambda ci: f"({cref(ci)} ? 1.f : 0.f)")
-                L.append(f"        const float t{i} = {expr};")
+        ref = lambda a: f"t{a}" if P.full[a] else f"q{a}"
+        for ph in range(nph):
+            emit_row_scalars(ph)
+            last = ph == nph - 1
+            reds = [i for i in reduces if P.phase[P.ssa[i][1]] == ph]
+            targets = [P.ssa[i][1] for i in reds]
+            out_full = [(k, o) for k, o in enumerate(P.outputs) if o.kind in ("full", "col")] if last else []
+            targets += [o.sid for _, o in out_full]
+            need = needed_for(targets)
             for i in reds:
-                L.append(f"        p{i} = {_RED_COMB[P.ssa[i][0][7:]].format(a=f'p{i}', b=ref(P.ssa[i][1]))};")
-            for k, o in out_full:
-                if o.kind == "full":
-                    L.append(f"        o{k}[e] = {ref(o.sid)};")
+                L.append(f"{ind2}float p{i} = {_RED_ID[P.ssa[i][0][7:]]};")
+            if need or out_full:
+                L.append(f"{ind2}#pragma unroll")
+                L.append(f"{ind2}for (int c = 0; c < C_; ++c) if (lc[c]) {{")
+                for k, o in out_full:
+                    if o.kind == "full":
+                        L.append(f"{ind2}  float o{k}[W_];")
+                used = {P.ssa[i][4] for i in need if P.ssa[i][0] == "leaf"}
+                for k in sorted(used & packed):
+                    # a fresh copy per phase that the compiler cannot relate to the other phases' copies: the operand
+                    # stays packed across the reduction instead of being kept unpacked (twice the registers)
+                    L.append(f"{ind2}  V4 z{k} = w{b}_{k}[c]; asm volatile(\"\" : \"+r\"(z{k}.x), \"+r\"(z{k}.y), \"+r\"(z{k}.z), \"+r\"(z{k}.w));")
+                L.append(f"{ind2}  #pragma unroll")
+                L.append(f"{ind2}  for (int e = 0; e < W_; ++e) {{")
+                for i in need:
+                    expr = G.ssa_line(i, ref, lambda k: leaf_ref(k, b), lambda ci: f"({cref(ci, b)} ? 1.f : 0.f)")
+                    L.append(f"{ind2}    const float t{i} = {expr};")
+                for i in reds:
+                    L.append(f"{ind2}    p{i} = {_RED_COMB[P.ssa[i][0][7:]].format(a=f'p{i}', b=ref(P.ssa[i][1]))};")
+                for k, o in out_full:
+                    if o.kind == "full":
+                        L.append(f"{ind2}    o{k}[e] = {ref(o.sid)};")
+                    else:
+                        L.append(f"{ind2}    acc{k}[c][e] = __fadd_rn(acc{k}[c][e], {ref(o.sid)});")
+                L.append(f"{ind2}  }}")
+                for k, o in out_full:
+                    if o.kind == "full":
+                        L.append(f"{ind2}  stv_{_DT[o.dtype]}<W_>(P.out[{k}].ptr, {rowvar} * R_ + (tr + c * T_) * W_, o{k});")
+                L.append(f"{ind2}}}")
+            for i in reds:
+                comb = _RED_COMB[P.ssa[i][0][7:]]
+                L.append(f"{ind2}#pragma unroll")
+                L.append(f"{ind2}for (int m = {min(T, 32) // 2}; m > 0; m >>= 1) p{i} = {comb.format(a=f'p{i}', b=f'__shfl_xor_sync(0xffffffffu, p{i}, m)')};")
+                if T > 32:
+                    L.append(f"{ind2}if ((threadIdx.x & 31) == 0) red_s[{reduces.index(i)}][threadIdx.x >> 5] = p{i};")
+            if reds and T > 32:
+                L.append(f"{ind2}__syncthreads();")
+            for i in reds:
+                if T > 32:
+                    rs, comb = reduces.index(i), _RED_COMB[P.ssa[i][0][7:]]
+                    L.append(f"{ind2}float q{i} = red_s[{rs}][0];")
+                    L.append(f"{ind2}#pragma unroll")
+                    L.append(f"{ind2}for (int w = 1; w < {T // 32}; ++w) q{i} = {comb.format(a=f'q{i}', b=f'red_s[{rs}][w]')};")
                 else:
-                    L.append(f"        acc{k}[c][e] = __fadd_rn(acc{k}[c][e], {ref(o.sid)});")
-            L.append("      }")
-            for k, o in out_full:
-                if o.kind == "full":
-                    L.append(f"      stv_{_DT[o.dtype]}<W_>(P.out[{k}].ptr, row * R_ + (tr + c * T_) * W_, o{k});")
-            L.append("    }")
-        for i in reds:
-            comb = _RED_COMB[P.ssa[i][0][7:]]
-            L.append("    #pragma unroll")
-            L.append(f"    for (int m = {min(T, 32) // 2}; m > 0; m >>= 1) p{i} = {comb.format(a=f'p{i}', b=f'__shfl_xor_sync(0xffffffffu, p{i}, m)')};")
-            if T > 32:
-                L.append(f"    if ((threadIdx.x & 31) == 0) red_s[{reduces.index(i)}][threadIdx.x >> 5] = p{i};")
-        if reds and T > 32:
-            L.append("    __syncthreads();")
-        for i in reds:
-            if T > 32:
-                rs, comb = reduces.index(i), _RED_COMB[P.ssa[i][0][7:]]
-                L.append(f"    float q{i} = red_s[{rs}][0];")
-                L.append("    #pragma unroll")
-                L.append(f"    for (int w = 1; w < {T // 32}; ++w) q{i} = {comb.format(a=f'q{i}', b=f'red_s[{rs}][w]')};")
-            else:
-                L.append(f"    const float q{i} = p{i};")
-            emitted_row.add(i)
-    emit_row_scalars(nph)
-    for k, o in enumerate(P.outputs):
-        if o.kind == "row":
-            L.append(f"    if (tr == 0) st1_{_DT[o.dtype]}(P.out[{k}].ptr, row, q{o.sid});")
-    if reduces and T > 32:
-        L.append("    __syncthreads();  // red_s is reused by the next row")
-    L.append("  }")
+                    L.append(f"{ind2}const float q{i} = p{i};")
+                emitted_row.add(i)
+        emit_row_scalars(nph)
+        for k, o in enumerate(P.outputs):
+            if o.kind == "row":
+                L.append(f"{ind2}if (tr == 0) st1_{_DT[o.dtype]}(P.out[{k}].ptr, {rowvar}, q{o.sid});")
+        if reduces and T > 32:
+            L.append(f"{ind2}__syncthreads();  // red_s is reused by the next row")
+        L.append(f"{ind}}}")
+
+    L.append(f"  const i64 STEP = (i64)gridDim.x * {RPC};")
+    L.append(f"  i64 row = (i64)blockIdx.x * {RPC} + rslot;")
+    if nbuf == 1:
+        L.append(f"  for (; row < {NR}; row += STEP) {{")
+        emit_load(0, "row", "    ")
+        emit_body(0, "row", "    ")
+        L.append("  }")
+    else:
+        L.append(f"  if (row < {NR}) {{")
+        emit_load(0, "row", "    ")
+        L.append("  }")
+        L.append(f"  while (row < {NR}) {{")
+        L.append("    const i64 nxt = row + STEP;")
+        L.append(f"    if (nxt < {NR}) {{")
+        emit_load(1, "nxt", "      ")
+        L.append("    }")
+        emit_body(0, "row", "    ")
+        L.append(f"    if (nxt >= {NR}) break;")
+        L.append("    row = nxt + STEP;")
+        L.append(f"    if (row < {NR}) {{")
+        emit_load(0, "row", "      ")
+        L.append("    }")
+        emit_body(1, "nxt", "    ")
+        L.append("  }")
     if cols:
         # partial column sums of every row slot of this CTA: scratch[col output][part][column]
         L.append("  #pragma unroll")
         L.append("  for (int c = 0; c < C_; ++c) if (lc[c]) {")
-        for j, k in enumerate(cols):
-            L.append(f"    stv_f32<W_>(P.scratch, ((i64){j} * P.nparts + (i64)blockIdx.x * {RPC} + rslot) * R_ + (tr + c * T_) * W_, acc{k}[c]);")
+        for j_, k in enumerate(cols):
+            L.append(f"    stv_f32<W_>(P.scratch, ((i64){j_} * P.nparts + (i64)blockIdx.x * {RPC} + rslot) * R_ + (tr + c * T_) * W_, acc{k}[c]);")
         L.append("  }")
     L.append("}")
     if cols:
         L.append('extern "C" __global__ void __launch_bounds__(256) rk_fold(const __grid_constant__ Params P) {')
         L.append("  const int col = blockIdx.x * 256 + threadIdx.x; if (col >= R_) return;")
-        for j, k in enumerate(cols):
+        for j_, k in enumerate(cols):
             dt = _DT[P.outputs[k].dtype]
-            L.append(f"  {{ float s = 0.f; const float* p = P.scratch + (i64){j} * P.nparts * R_ + col;")
+            L.append(f"  {{ float s = 0.f; const float* p = P.scratch + (i64){j_} * P.nparts * R_ + col;")
             L.append("    for (int i = 0; i < P.nparts; ++i) s = __fadd_rn(s, p[(i64)i * R_]);")
             L.append(f"    st1_{dt}(P.out[{k}].ptr, col, s); }}")
         L.append("}")

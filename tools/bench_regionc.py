@@ -46,6 +46,9 @@ def time_region(region, ins, outs, iters=20):
         if r.data_ptr() not in seen:
             seen.add(r.data_ptr())
             nbytes += r.numel() * r.element_size()
+    if os.environ.get("B200_PROFILE"):  # under ncu: one launch per region is all that is wanted
+        torch.cuda.synchronize()
+        return float("nan"), nbytes
     for i in range(3):
         region(*sets[i % NSETS])
     torch.cuda.synchronize()
