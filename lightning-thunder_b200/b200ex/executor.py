@@ -870,6 +870,69 @@ ex.register_supported(b200_swiglu.id, _swiglu_check, grad_transform=_swiglu_grad
 ex.register_supported(b200_swiglu_bwd.id)
 
 
+# ---- data-parallel gradient synchronisation ---------------------------------------------
+# The reference's rule (thunder/distributed/prims.py:396-420) pre-scales every gradient, `g / world`, and then reduces
+# with SUM: one extra elementwise pass over the FULL gradient per parameter (227 launches and 2 x 16 GB of HBM traffic
+# per Llama-3-8B step) in front of each collective.  NCCL averages inside the collective (ncclAvg), so with an NCCL
+# group the b200 rule hands the raw gradient to reduce_scatter / all_reduce with AVG: no launch, no bytes.  Other
+# backends (gloo has no AVG) keep the reference's spelling.  Forward and collectives are the reference's own prims.
+def _sync_uses_avg(group) -> bool:
+    try:
+        return "nccl" in str(torch.distributed.get_backend(group)).lower()
+    except Exception:
+        return False
+
+
+def _synchronize_check(a, group, distparallel_type) -> bool:
+    from thunder.core.proxies import DistParallelType
+
+    return isinstance(a, TensorProxy) and distparallel_type in (DistParallelType.FULLY_SHARDED, DistParallelType.REPLICATED)
+
+
+def _synchronize_fwd(a, group, distparallel_type):
+    import thunder.distributed.prims as dist_prims
+    from thunder.core.proxies import DistParallelType
+
+    if distparallel_type == DistParallelType.FULLY_SHARDED:
+        return dist_prims.all_gather(a, group, True).wait()
+    return prims.shallow_copy(a)
+
+
+def _synchronize_grad(a, group, distparallel_type):
+    import thunder.distributed.prims as dist_prims
+    from thunder.core.proxies import DistParallelType
+    from thunder.distributed import get_skip_data_parallel_grad_sync
+
+    out = _synchronize_fwd(a, group, distparallel_type)
+    g = get_grad(out)
+    if get_skip_data_parallel_grad_sync() and distparallel_type == DistParallelType.REPLICATED:
+        put_grads((a,), (g,))
+        return out
+    ops_ = dist_prims.DistributedReduceOps
+    if _sync_uses_avg(group):
+        op, src = ops_.AVG, g
+    else:
+        op, src = ops_.SUM, g / group.size()
+    if distparallel_type == DistParallelType.FULLY_SHARDED:
+        synced = dist_prims.reduce_scatter(src, op, group, do_async=True).wait()
+    else:
+        synced = dist_prims.all_reduce(src, op, group, do_async=True).wait()
+    put_grads((a,), (synced,))
+    return out
+
+
+def _register_synchronize() -> None:
+    try:
+        import thunder.distributed.prims as dist_prims
+    except Exception:  # torch.distributed not available: nothing to synchronise
+        return
+    ex.register_supported(dist_prims.PrimIDs.SYNCHRONIZE, _synchronize_check, execution_transform=_synchronize_fwd, grad_transform=_synchronize_grad)
+
+
+if os.environ.get("B200EX_SYNC_RULE", "1") != "0":
+    _register_synchronize()
+
+
 _MACRO_IMPL: dict[Any, Callable] = {
     b200_rms_norm_fwd.id: _rms_norm_fwd_impl,
     b200_rms_norm_bwd.id: _rms_norm_bwd_impl,

@@ -728,6 +728,17 @@ def compile_component(inputs: dict, nodes: list, outputs: list) -> list:
             want.append(src)
 
     kinds = {n.out: _classify_reduce(n, meta) for n in nodes if n.op == "reduce"}
+    # a column sum whose only use is a dtype conversion is folded straight into that dtype (ltorch.sum of a 16-bit
+    # tensor is convert -> sum -> convert): the fold kernel rounds once, no extra launch
+    for o in [o for o, k in kinds.items() if k == "col" and o not in outputs]:
+        users = [n for n in nodes if any(isinstance(a, str) and a == o for a in n.args)]
+        if len(users) == 1 and users[0].op == "convert":
+            cv, red = users[0], producer[o]
+            merged = Node("reduce", cv.out, cv.dtype, cv.shape, red.args, red.attrs)
+            nodes = [merged if n is red else n for n in nodes if n is not cv]
+            producer = {n.out: n for n in nodes}
+            meta[cv.out] = (cv.dtype, tuple(cv.shape))
+            kinds[cv.out] = kinds.pop(o)
     cols = [o for o, k in kinds.items() if k == "col"]
     # everything downstream of a column sum waits for the fold: second stage
     after = set()
@@ -818,6 +829,8 @@ __device__ __forceinline__ float h2f(u32 h) { float f; asm("{.reg .b16 t; cvt.u1
 __device__ __forceinline__ u32 f2h2(float lo, float hi) { u32 r; asm("cvt.rn.f16x2.f32 %%0, %%1, %%2;" : "=r"(r) : "f"(hi), "f"(lo)); return r; }
 __device__ __forceinline__ float rnd_bf16(float x) { return __uint_as_float(f2bf2(x, 0.f) << 16); }
 __device__ __forceinline__ float rnd_f16(float x) { return h2f(f2h2(x, 0.f) & 0xffffu); }
+__device__ __forceinline__ void rnd_bf16_2(float a, float b, float& x, float& y) { const u32 p = f2bf2(a, b); x = __uint_as_float(p << 16); y = __uint_as_float(p & 0xffff0000u); }
+__device__ __forceinline__ void rnd_f16_2(float a, float b, float& x, float& y) { const u32 p = f2h2(a, b); x = h2f(p & 0xffffu); y = h2f(p >> 16); }
 __device__ __forceinline__ float nanmax(float a, float b) { return (a != a || b != b) ? __int_as_float(0x7fc00000) : fmaxf(a, b); }
 __device__ __forceinline__ float nanmin(float a, float b) { return (a != a || b != b) ? __int_as_float(0x7fc00000) : fminf(a, b); }
 __device__ __forceinline__ float sgn(float a) { return a > 0.f ? 1.f : (a < 0.f ? -1.f : a); }
@@ -960,6 +973,32 @@ class _Gen:
     def leaf_estride(self, k):
         return str(dict(self.leaf_aff(k)[0]).get(self.vd, 0))
 
+    def emit_elements(self, L, ind, W, ids, ref, leafref, predref, tail):
+        """The per-element loop: values `ids` for every element of the chunk, two elements per trip so that roundings
+        to a 16-bit format convert a pair at once (one cvt.rn.x2 instead of two).  ref(a, lane) names an operand,
+        leafref(k, e) reads element e of leaf k, tail(lane, e) -> extra lines per element (stores, partial sums)."""
+        lanes = [("_0", "e"), ("_1", "e + 1")] if W >= 2 else [("", "e")]
+        L.append(f"{ind}#pragma unroll")
+        L.append(f"{ind}for (int e = 0; e < {W}; e += {len(lanes)}) {{")
+        for i in ids:
+            op, a, b, c, imm = self.P.ssa[i]
+            if op in ("rnd_bf16", "rnd_f16") and len(lanes) == 2:
+                L.append(f"{ind}  float t{i}_0, t{i}_1; {op}_2({ref(a, '_0')}, {ref(a, '_1')}, t{i}_0, t{i}_1);")
+                continue
+            for suf, e in lanes:
+                if op == "leaf":
+                    expr = leafref(imm, e)
+                elif op == "const":
+                    expr = f"__uint_as_float(0x{imm:08x}u)"
+                elif op == "pred":
+                    expr = predref(imm)
+                else:
+                    expr = _EXPR[op].format(a=ref(a, suf), b=ref(b, suf), c=ref(c, suf))
+                L.append(f"{ind}  const float t{i}{suf} = {expr};")
+        for suf, e in lanes:
+            L.extend(f"{ind}  {line}" for line in tail(suf, e))
+        L.append(f"{ind}}}")
+
     def ssa_line(self, i, ref, leafref, predref):
         op, a, b, c, imm = self.P.ssa[i]
         if op == "leaf":
@@ -1020,14 +1059,42 @@ def _fold(P: Program, assume: dict):
     def R(x):
         return res[x] if x >= 0 else None
 
+    NZERO = _f32_bits(-0.0)
+    # which 16-bit formats every value is exactly representable in: rounding such a value again is the identity
+    # (`-x` of a bf16 x, a `where` between bf16 values, a sum whose other operand is a zero pad, ...)
+    fits: list = []
+    small = {ZERO: {"bf16", "f16"}, NZERO: {"bf16", "f16"}, ONE: {"bf16", "f16"}, _f32_bits(-1.0): {"bf16", "f16"}}
+
+    def F(x):
+        r_ = res[x]
+        return small.get(r_[1], set()) if r_[0] == "k" else fits[r_[1]]
+
     for i, (op, a, b, c, imm) in enumerate(P.ssa):
         r = ("v", i)
+        fit: set = set()
         if op == "const":
             r = ("k", imm)
         elif op == "pred" and imm in assume:
             r = ("k", ONE if assume[imm] else ZERO)
+        elif op == "pred":
+            fit = {"bf16", "f16"}
         elif op == "leaf" and any(assume.get(ci) is False for ci in P.leaves[imm].guard):
             r = ("k", ZERO)
+        elif op == "leaf":
+            fit = {"bf16": {"bf16"}, "f16": {"f16"}, "bool": {"bf16", "f16"}}.get(_DT[P.leaves[imm].dtype], set())
+        elif op in ("rnd_bf16", "rnd_f16"):
+            kind = op[4:]
+            if kind in F(a):
+                r = R(a)
+            fit = {kind}
+        elif op in ("neg", "abs", "mov"):
+            fit = set(F(a))
+        elif op in ("maximum", "minimum"):
+            fit = F(a) & F(b)
+        elif op in COMPARE or op in ("not", "or", "sign"):
+            fit = {"bf16", "f16"}
+        elif op == "add" and (R(a) in (("k", ZERO), ("k", NZERO)) or R(b) in (("k", ZERO), ("k", NZERO))):
+            r = R(b) if R(a) in (("k", ZERO), ("k", NZERO)) else R(a)  # x + 0 (a zero pad on the other side of a cat)
         elif op == "and":
             ra, rb = R(a), R(b)
             if ra == ("k", ZERO) or rb == ("k", ZERO):
@@ -1039,8 +1106,12 @@ def _fold(P: Program, assume: dict):
         elif op == "where":
             rc = R(a)
             if rc[0] == "k":
-                r = R(b) if rc[1] != ZERO and rc[1] != _f32_bits(-0.0) else R(c)
+                r = R(b) if rc[1] != ZERO and rc[1] != NZERO else R(c)
+            fit = F(b) & F(c)
+        if op == "and":
+            fit = {"bf16", "f16"}
         res.append(r)
+        fits.append(F(i) if r != ("v", i) else fit)
     live, undecided = set(), set()
     stack = [o.sid for o in P.outputs]
     while stack:
@@ -1120,19 +1191,13 @@ def generate_flat(P: Program, modes: tuple, unroll: int) -> str:
     def math_and_store(res, live, ind, leafref):
         for k in range(len(P.outputs)):
             L.append(f"{ind}float o{k}[{W}];")
-        L.append(f"{ind}#pragma unroll")
-        L.append(f"{ind}for (int e = 0; e < {W}; ++e) {{")
 
-        def ref(a):
+        def ref(a, suf):
             r = res[a]
-            return f"__uint_as_float(0x{r[1]:08x}u)" if r[0] == "k" else f"t{r[1]}"
+            return f"__uint_as_float(0x{r[1]:08x}u)" if r[0] == "k" else f"t{r[1]}{suf}"
 
-        for i in sorted(live):
-            expr = G.ssa_line(i, ref, leafref, lambda ci: f"(cn[u][{ci}] ? 1.f : 0.f)")
-            L.append(f"{ind}  const float t{i} = {expr};")
-        for k, o in enumerate(P.outputs):
-            L.append(f"{ind}  o{k}[e] = {ref(o.sid)};")
-        L.append(f"{ind}}}")
+        tail = lambda suf, e: [f"o{k}[{e}] = {ref(o.sid, suf)};" for k, o in enumerate(P.outputs)]
+        G.emit_elements(L, ind, W, sorted(live), ref, leafref, lambda ci: f"(cn[u][{ci}] ? 1.f : 0.f)", tail)
         for k, o in enumerate(P.outputs):
             L.append(f"{ind}stv_{_DT[o.dtype]}<{W}>(P.out[{k}].ptr, {out_off}, o{k});")
 
@@ -1149,7 +1214,7 @@ def generate_flat(P: Program, modes: tuple, unroll: int) -> str:
         L.append("    }")
         L.append("    #pragma unroll")
         L.append(f"    for (int u = 0; u < {U}; ++u) if (live[u]) {{")
-        math_and_store(res, live, "      ", lambda k: f"v[u][{k}][e]")
+        math_and_store(res, live, "      ", lambda k, e: f"v[u][{k}][{e}]")
         L.append("    }")
     else:
         blocks = [0]
@@ -1164,7 +1229,7 @@ def generate_flat(P: Program, modes: tuple, unroll: int) -> str:
                 for k in sorted(P.ssa[i][4] for i in live if P.ssa[i][0] == "leaf"):
                     L.append(f"{ind}  float v{k}[{W}];")
                     L.append(load(k, ind + "  ", f"v{k}"))
-                math_and_store(res, live, ind + "  ", lambda k: f"v{k}[e]")
+                math_and_store(res, live, ind + "  ", lambda k, e: f"v{k}[{e}]")
                 L.append(f"{ind}}}")
                 return
             ci = min(und)
@@ -1236,7 +1301,10 @@ def generate_row(P: Program, modes: tuple) -> str:
     packed = {k for k in per_row if modes[k][0] == "v" and modes[k][1] in ("bf16", "f16") and W == 8}
     cost = sum(C * (4 if k in packed else W) for k in per_row)
     fixed = (len(hoisted) + len(cols)) * C * W
-    nbuf = 2 if (per_row and 2 * cost + fixed <= 150 and os.environ.get("B200EX_ROW_PREFETCH", "1") != "0") else 1
+    # the second buffer pays when a row's critical path is long (several operands, a column sum, several reductions);
+    # a two-operand single-reduction row (RMSNorm forward) is already at the HBM limit without it
+    worth = len(per_row) >= 3 or bool(cols) or nph >= 3
+    nbuf = 2 if (worth and 2 * cost + fixed <= 150 and os.environ.get("B200EX_ROW_PREFETCH", "1") != "0") else 1
 
     names_i = lambda b: [f"xo{b}[{k}]" for k in range(no)] + [f"xi[c][{k - no}]" for k in range(no, nv)]
     names_r = lambda b: [f"xo{b}[{k}]" for k in range(no)] + ["0"] * n_inner
@@ -1261,12 +1329,16 @@ def generate_row(P: Program, modes: tuple) -> str:
         out.append(f"{ind}}}")
         return out
 
-    def leaf_ref(k, b):
+    def leaf_ref(k, b, e="e"):
         if k in hoisted:
-            return f"vh{k}[c][e]"
+            return f"vh{k}[c][{e}]"
         if k in packed:
-            return f"unp_{modes[k][1]}(z{k}, e)"
-        return f"v{b}_{k}[c][e]"
+            return f"unp_{modes[k][1]}(z{k}, {e})"
+        return f"v{b}_{k}[c][{e}]"
+
+    # identities known without any condition decided (re-rounding an exact value, x + 0): res[i] names what value i is
+    res, _, _ = _fold(P, {})
+    rid = lambda a: res[a][1] if res[a][0] == "v" else None  # resolved ssa id, None for a constant
 
     L = [G.head(len(in_names))]
     L.append("__device__ __forceinline__ float unp_bf16(const V4& v, int e) { const u32 w = (e >> 1) == 0 ? v.x : ((e >> 1) == 1 ? v.y : ((e >> 1) == 2 ? v.z : v.w)); return (e & 1) ? __uint_as_float(w & 0xffff0000u) : __uint_as_float(w << 16); }")
@@ -1340,14 +1412,18 @@ def generate_row(P: Program, modes: tuple) -> str:
             L.extend(load_full(k, b, ind, f"w{b}_{k}" if k in packed else f"v{b}_{k}"))
 
     def needed_for(targets):
+        """Values that vary inside the row and must be evaluated in the element loop to produce `targets`."""
         need, stack = set(), list(targets)
         while stack:
-            i = stack.pop()
-            if i in need or not P.full[i]:
+            i = rid(stack.pop())
+            if i is None or i in need or not P.full[i]:
                 continue
             need.add(i)
             stack.extend(x for x in P.ssa[i][1:4] if x >= 0)
         return sorted(need)
+
+    def konst(a):
+        return f"__uint_as_float(0x{res[a][1]:08x}u)"
 
     def emit_body(b, rowvar, ind):
         L.append(f"{ind}{{")
@@ -1356,13 +1432,19 @@ def generate_row(P: Program, modes: tuple) -> str:
 
         def emit_row_scalars(upto_phase):
             for i, s_ in enumerate(P.ssa):
-                if P.full[i] or i in emitted_row or P.phase[i] > upto_phase or s_[0].startswith("reduce_"):
+                if P.full[i] or i in emitted_row or P.phase[i] > upto_phase or s_[0].startswith("reduce_") or rid(i) != i:
                     continue
-                expr = G.ssa_line(i, lambda a: f"q{a}", lambda k: f"s{b}_{k}", lambda ci: f"(cr{b}_{ci} ? 1.f : 0.f)")
+                qref = lambda a: konst(a) if rid(a) is None else f"q{rid(a)}"
+                expr = G.ssa_line(i, qref, lambda k: f"s{b}_{k}", lambda ci: f"(cr{b}_{ci} ? 1.f : 0.f)")
                 L.append(f"{ind2}const float q{i} = {expr};")
                 emitted_row.add(i)
 
-        ref = lambda a: f"t{a}" if P.full[a] else f"q{a}"
+        def ref(a, suf=""):
+            i = rid(a)
+            if i is None:
+                return konst(a)
+            return f"t{i}{suf}" if P.full[i] else f"q{i}"
+
         for ph in range(nph):
             emit_row_scalars(ph)
             last = ph == nph - 1
@@ -1384,19 +1466,17 @@ def generate_row(P: Program, modes: tuple) -> str:
                     # a fresh copy per phase that the compiler cannot relate to the other phases' copies: the operand
                     # stays packed across the reduction instead of being kept unpacked (twice the registers)
                     L.append(f"{ind2}  V4 z{k} = w{b}_{k}[c]; asm volatile(\"\" : \"+r\"(z{k}.x), \"+r\"(z{k}.y), \"+r\"(z{k}.z), \"+r\"(z{k}.w));")
-                L.append(f"{ind2}  #pragma unroll")
-                L.append(f"{ind2}  for (int e = 0; e < W_; ++e) {{")
-                for i in need:
-                    expr = G.ssa_line(i, ref, lambda k: leaf_ref(k, b), lambda ci: f"({cref(ci, b)} ? 1.f : 0.f)")
-                    L.append(f"{ind2}    const float t{i} = {expr};")
-                for i in reds:
-                    L.append(f"{ind2}    p{i} = {_RED_COMB[P.ssa[i][0][7:]].format(a=f'p{i}', b=ref(P.ssa[i][1]))};")
-                for k, o in out_full:
-                    if o.kind == "full":
-                        L.append(f"{ind2}    o{k}[e] = {ref(o.sid)};")
-                    else:
-                        L.append(f"{ind2}    acc{k}[c][e] = __fadd_rn(acc{k}[c][e], {ref(o.sid)});")
-                L.append(f"{ind2}  }}")
+
+                def tail(suf, e, reds=reds, out_full=out_full):
+                    lines = [f"p{i} = {_RED_COMB[P.ssa[i][0][7:]].format(a=f'p{i}', b=ref(P.ssa[i][1], suf))};" for i in reds]
+                    for k, o in out_full:
+                        if o.kind == "full":
+                            lines.append(f"o{k}[{e}] = {ref(o.sid, suf)};")
+                        else:
+                            lines.append(f"acc{k}[c][{e}] = __fadd_rn(acc{k}[c][{e}], {ref(o.sid, suf)});")
+                    return lines
+
+                G.emit_elements(L, ind2 + "  ", W, need, ref, lambda k, e: leaf_ref(k, b, e), lambda ci: f"({cref(ci, b)} ? 1.f : 0.f)", tail)
                 for k, o in out_full:
                     if o.kind == "full":
                         L.append(f"{ind2}  stv_{_DT[o.dtype]}<W_>(P.out[{k}].ptr, {rowvar} * R_ + (tr + c * T_) * W_, o{k});")
@@ -1421,7 +1501,7 @@ def generate_row(P: Program, modes: tuple) -> str:
         emit_row_scalars(nph)
         for k, o in enumerate(P.outputs):
             if o.kind == "row":
-                L.append(f"{ind2}if (tr == 0) st1_{_DT[o.dtype]}(P.out[{k}].ptr, {rowvar}, q{o.sid});")
+                L.append(f"{ind2}if (tr == 0) st1_{_DT[o.dtype]}(P.out[{k}].ptr, {rowvar}, {ref(o.sid)});")
         if reduces and T > 32:
             L.append(f"{ind2}__syncthreads();  // red_s is reused by the next row")
         L.append(f"{ind}}}")
@@ -1459,13 +1539,20 @@ def generate_row(P: Program, modes: tuple) -> str:
         L.append("  }")
     L.append("}")
     if cols:
+        # fold of the per-CTA partials: 32 columns x 8 slices of the partials per CTA, fixed order (deterministic)
         L.append('extern "C" __global__ void __launch_bounds__(256) rk_fold(const __grid_constant__ Params P) {')
-        L.append("  const int col = blockIdx.x * 256 + threadIdx.x; if (col >= R_) return;")
+        L.append("  __shared__ float part[8][33];")
+        L.append("  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5, col = blockIdx.x * 32 + lane;")
         for j_, k in enumerate(cols):
             dt = _DT[P.outputs[k].dtype]
             L.append(f"  {{ float s = 0.f; const float* p = P.scratch + (i64){j_} * P.nparts * R_ + col;")
-            L.append("    for (int i = 0; i < P.nparts; ++i) s = __fadd_rn(s, p[(i64)i * R_]);")
-            L.append(f"    st1_{dt}(P.out[{k}].ptr, col, s); }}")
+            L.append("    if (col < R_) for (int i = g; i < P.nparts; i += 8) s = __fadd_rn(s, p[(i64)i * R_]);")
+            L.append("    part[g][lane] = s; __syncthreads();")
+            L.append("    if (g == 0 && col < R_) { float t = part[0][lane];")
+            L.append("      #pragma unroll")
+            L.append("      for (int w = 1; w < 8; ++w) t = __fadd_rn(t, part[w][lane]);")
+            L.append(f"      st1_{dt}(P.out[{k}].ptr, col, t); }}")
+            L.append("    __syncthreads(); }")
         L.append("}")
     return "\n".join(L)
 
@@ -1605,5 +1692,5 @@ class RegionLaunch:
                     prm.scratch = scratch.data_ptr()
                 kernel.launch(kernel.main, prm, grid, block, stream)
                 if ncol:
-                    kernel.launch(kernel.fold, prm, (P.row_len + 255) // 256, 256, stream)
+                    kernel.launch(kernel.fold, prm, (P.row_len + 31) // 32, 256, stream)
         return result
