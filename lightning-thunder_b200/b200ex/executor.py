@@ -143,6 +143,9 @@ class B200Executor(FusionExecutor):
         fuel = os.getenv("B200EX_OPTIMIZATION_FUEL")
         self.set_fuel(int(fuel) if fuel else FUEL_LEVEL.UNLIMITED)
         self._use_rematerialization = True
+        import threading
+
+        self._tls = threading.local()
 
     # -- optimization fuel (extend/__init__.py:201-226; nvfuserex_impl.py:658-675) ----------------
     def get_fuel(self, amount: int = 1, /) -> bool:
@@ -160,6 +163,32 @@ class B200Executor(FusionExecutor):
         if not isinstance(value, int) or value < 0:
             raise ValueError(f"optimization fuel must be a non-negative int, got {value!r}")
         self._optimization_fuel = value
+
+    # -- op-level rules apply only where their checker accepts --------------------------------------------
+    # The reference asks "can this executor execute OR fuse the symbol" before it takes the executor's transform
+    # (core/transforms.py:1506-1510 for grad transforms, executors/passes.py:56-59 for execution transforms), and
+    # `can_fuse` of a composite is true as soon as all of its subsymbols are claimable (extend/__init__.py:101-117).
+    # With layout and reduction prims in the vocabulary that holds for e.g. a `layer_norm` over two dims or a
+    # `softmax` over dim 0 — which the op-level kernels do not cover and their checkers decline.  Such a symbol must
+    # take the default path (decomposition, default VJP rules) and reach the fusion pass as prims.
+    def can_execute_or_fuse(self, bsym: BoundSymbol) -> bool:
+        direct = self.can_execute(bsym)
+        self._tls.direct = direct
+        return direct or self.can_fuse(bsym)
+
+    def get_grad_transform(self, sym):
+        # called right after can_execute_or_fuse(bsym) for the same bound symbol
+        if not getattr(self._tls, "direct", True):
+            return None
+        return super().get_grad_transform(sym)
+
+    def get_execution_transform(self, bsym: BoundSymbol):
+        impl = self.implmap.get(bsym.sym.id, None)
+        if impl is None or impl.execution_transform is None:
+            return None
+        if impl.checker is not None and not impl.checker(*bsym.args, **bsym.kwargs):
+            return None
+        return impl.execution_transform
 
     # -- region construction ------------------------------------------------------------------------
     def flatten(self, bsym: BoundSymbol) -> list[BoundSymbol]:
@@ -441,7 +470,7 @@ def _squeeze_check(a, dims) -> bool:
 def _reduce_check(a, dims, **kwargs) -> bool:
     # like the reference's _reduction_check (nvfuserex_impl.py:2112-2115): tensors of at least fp32 — ltorch upcasts
     # 16-bit inputs before it reduces, so that is what arrives here
-    if not (_rc_tensor(a) and _tdtype(a.dtype) is torch.float32 and _ints(dims) and len(dims) > 0):
+    if not (_rc_tensor(a) and a.ndim >= 1 and _tdtype(a.dtype) is torch.float32 and _ints(dims) and len(dims) > 0):
         return False
     corr = kwargs.get("correction", 0)
     return isinstance(corr, (int, float)) and not isinstance(corr, Proxy)
@@ -1048,7 +1077,14 @@ class B200Region:
         self.input_names = [p.name for p in inputs]
         self.output_names = [p.name for p in outputs]
         self.alias: dict[str, str] = {}
-        self.steps = self._lower()
+        try:
+            self.steps = self._lower()
+        except PwUnsupported:
+            raise
+        except Exception as e:  # a defect of the lowering must not take the user's compilation down with it
+            if os.environ.get("B200EX_STRICT"):
+                raise
+            raise PwUnsupported(f"{name}: internal lowering error, region declined ({type(e).__name__}: {e})") from e
         self.launch_kinds = [s.kind for s in self.steps if s.kind != "view"]
 
     def __repr__(self):

@@ -41,7 +41,14 @@ class _Group:
         self.table = torch.empty(n, 5, dtype=torch.int64, device=device)
         self.chunk_tensor = torch.tensor(tensor_of, dtype=torch.int32, device=device)
         self.chunk_index = torch.tensor(index_of, dtype=torch.int32, device=device)
-        self.ptrs = [p.data_ptr() for p in params]
+        self.ptrs = _table_key(params, states)
+
+
+def _table_key(params, states) -> list:
+    """What the cached device table depends on: the addresses of the parameters AND of their moments.
+    ``load_state_dict`` / ``state.clear()`` replace the moment tensors; a table keyed on the parameters alone would
+    keep updating the old ones."""
+    return [(p.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()) for p, st in zip(params, states)]
 
 
 class AdamW(torch.optim.Optimizer):
@@ -79,6 +86,11 @@ class AdamW(torch.optim.Optimizer):
             beta1, beta2 = group["betas"]
             for (device, dtype), params in buckets.items():
                 states = [self._state_for(p) for p in params]
+                for p, st in zip(params, states):
+                    for k in ("exp_avg", "exp_avg_sq"):
+                        m = st[k]
+                        if m.device != p.device or m.dtype != p.dtype or m.shape != p.shape or not m.is_contiguous():
+                            raise RuntimeError(f"b200ex.optim.AdamW: state '{k}' must be a contiguous tensor of the parameter's shape, dtype and device")
                 steps = {float(st["step"]) for st in states}
                 if len(steps) != 1:
                     raise RuntimeError("b200ex.optim.AdamW: parameters of one group must share their step count")
@@ -87,7 +99,7 @@ class AdamW(torch.optim.Optimizer):
                     st["step"] += 1
                 key = (gi, device, dtype)
                 g = self._groups.get(key)
-                if g is None or g.ptrs != [p.data_ptr() for p in params]:
+                if g is None or g.ptrs != _table_key(params, states):
                     g = self._groups[key] = _Group(params, states, device, dtype)
                 host, ev = g.hosts[g.turn], g.events[g.turn]
                 if ev is not None:

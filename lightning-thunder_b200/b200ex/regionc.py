@@ -1146,7 +1146,7 @@ def generate_flat(P: Program, modes: tuple, unroll: int) -> str:
     total = math.prod(ext) // W
     it = "u32" if math.prod(ext) < 2**31 else "i64"
     _, _, und0 = _fold(P, {})
-    U = unroll if not und0 else 1
+    U = unroll
     L.append('extern "C" __global__ void __launch_bounds__(256) rk_main(const __grid_constant__ Params P) {')
     L.append(f"  const {it} TOTAL = {total};")
     L.append(f"  for ({it} base = ({it})blockIdx.x * {256 * U} + threadIdx.x; base < TOTAL; base += ({it})gridDim.x * {256 * U}) {{")
@@ -1584,6 +1584,18 @@ class _Kernel:
         (self.main,) = jit._check(driver.cuModuleGetFunction(self.module, b"rk_main"), "cuModuleGetFunction")
         self.fold = jit._check(driver.cuModuleGetFunction(self.module, b"rk_fold"), "cuModuleGetFunction")[0] if has_fold else None
         self.launches = 0
+        self._occ: dict = {}
+
+    def ctas_per_sm(self, block: int) -> int:
+        """Resident CTAs per SM for `rk_main` at this block size.  Persistent grids are sized with it: a grid that is
+        not a whole number of resident waves leaves part of the GPU idle for the last one."""
+        if block not in self._occ:
+            try:
+                (n,) = jit._check(self.driver.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.main, block, 0), "cuOccupancyMaxActiveBlocksPerMultiprocessor")
+                self._occ[block] = max(1, int(n))
+            except Exception:
+                self._occ[block] = 4
+        return self._occ[block]
 
     def launch(self, func, params, grid, block, stream):
         argv = (ctypes.c_void_p * 1)(ctypes.addressof(params))
@@ -1594,6 +1606,10 @@ class _Kernel:
 
 
 def flat_unroll(P: Program) -> int:
+    """Work items per thread and trip of a flat kernel.  Several only for straight-line programs (all loads of all
+    items are issued first); a program with `cat` / `pad` branches takes one item at a time."""
+    if _fold(P, {})[2]:
+        return 1
     n = len(P.leaves)
     return 4 if n <= 2 else (2 if n <= 5 else 1)
 
@@ -1678,13 +1694,13 @@ class RegionLaunch:
             if P.kind == "flat":
                 U = flat_unroll(P)
                 items = math.prod(P.ext) // P.W
-                grid = max(1, min((items + 256 * U - 1) // (256 * U), sms * 8))
+                grid = max(1, min((items + 256 * U - 1) // (256 * U), sms * kernel.ctas_per_sm(256)))
                 kernel.launch(kernel.main, prm, grid, 256, stream)
             else:
                 T, C, RPC, block = row_geometry(P)
                 ncol = sum(1 for o in P.outputs if o.kind == "col")
                 groups = (P.n_rows + RPC - 1) // RPC
-                grid = max(1, min(groups, sms * (2 if ncol else 4)))
+                grid = max(1, min(groups, sms * kernel.ctas_per_sm(block)))
                 scratch = None
                 if ncol:
                     prm.nparts = grid * RPC

@@ -50,14 +50,28 @@ adamw_kernel(const b200k_adam_tensor* __restrict__ table, const int32_t* __restr
         T* m = static_cast<T*>(t.exp_avg);
         T* v = static_cast<T*>(t.exp_avg_sq);
         const int64_t vec0 = static_cast<int64_t>(chunk_index[c]) * kAdamChunkVecs;
+        // 16-byte access needs all four tensors on 16-byte addresses; an offset view (a shard of a flat buffer, a DDP
+        // bucket view, p[1:]) is updated element by element instead
+        const bool aligned = ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+                               reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+        if (!aligned) {
+            const int64_t e0 = vec0 * kE, e1 = e0 + kAdamChunkVecs * kE < t.numel ? e0 + kAdamChunkVecs * kE : t.numel;
+            for (int64_t i = e0 + threadIdx.x; i < e1; i += kAdamThreads) {
+                float pf = V::load1(p, i), mf = V::load1(m, i), vf = V::load1(v, i);
+                adam_math(pf, V::load1(g, i), mf, vf, a);
+                V::store1(p, i, pf), V::store1(m, i, mf), V::store1(v, i, vf);
+            }
+            continue;
+        }
         const int64_t nvec = t.numel / kE;  // whole vectors; the tail (< kE elements) is handled below
         uint4 pv[kAdamVpt], gv[kAdamVpt], mv[kAdamVpt], vv[kAdamVpt];
 #pragma unroll
         for (int k = 0; k < kAdamVpt; ++k) {
             const int64_t i = vec0 + threadIdx.x + k * kAdamThreads;
             if (i < nvec) {
-                pv[k] = ld_stream(p + i * kE), gv[k] = ld_stream(g + i * kE);
-                mv[k] = ld_stream(m + i * kE), vv[k] = ld_stream(v + i * kE);
+                // p, m, v are rewritten below: plain (coherent) loads; only the gradient is read-only here
+                pv[k] = ld_stream_rw(p + i * kE), gv[k] = ld_stream(g + i * kE);
+                mv[k] = ld_stream_rw(m + i * kE), vv[k] = ld_stream_rw(v + i * kE);
             }
         }
 #pragma unroll

@@ -30,6 +30,16 @@ __device__ __forceinline__ uint4 ld_stream(const void* p) {
                  : "l"(p));
     return r;
 }
+// ld_stream_rw: like ld_stream for buffers the same kernel also writes (in-place updates): the non-coherent
+// (.nc) path is only defined for data that stays read-only for the whole kernel.
+__device__ __forceinline__ uint4 ld_stream_rw(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
 __device__ __forceinline__ uint4 ld_keep(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 __device__ __forceinline__ void st_stream(void* p, const uint4& v) {
     asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)

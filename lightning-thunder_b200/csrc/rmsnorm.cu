@@ -616,7 +616,6 @@ constexpr int kBwdRows = 2;
 // Backward tuning knobs, read once from the environment (A/B measurements only):
 //   B200K_RMSNORM_BWD_TMA=0      use the register-resident kernel instead of the TMA-staged one
 //   B200K_RMSNORM_BWD_VPL=1|2    16-byte vectors per thread
-//   B200K_RMSNORM_BWD_ROWS=1|2   rows per pipeline stage
 //   B200K_RMSNORM_BWD_CTAS=1|2   resident CTAs per SM (splits the shared-memory ring)
 struct TmaTune {
     bool enabled;
@@ -631,7 +630,7 @@ TmaTune tma_tune() {
         TmaTune r;
         r.enabled = geti("B200K_RMSNORM_BWD_TMA", 1) != 0;
         r.vpl = geti("B200K_RMSNORM_BWD_VPL", 1);
-        r.rows = geti("B200K_RMSNORM_BWD_ROWS", 2);
+        r.rows = kBwdRows;  // fixed: the partial-sum scratch (b200k_rmsnorm_bwd_scratch_bytes) is sized for two rows per stage
         r.ctas_per_sm = geti("B200K_RMSNORM_BWD_CTAS", 1);
         if (r.vpl != 1 && r.vpl != 2) r.vpl = 1;
         if (r.rows != 1 && r.rows != 2) r.rows = 2;

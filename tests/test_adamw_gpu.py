@@ -82,3 +82,62 @@ def test_rejects_what_it_cannot_do():
     p.grad = torch.randn(8)
     with pytest.raises(RuntimeError, match="CUDA"):
         AdamW([p]).step()
+
+
+def test_load_state_dict_after_a_step_switches_to_the_loaded_moments():
+    """step, load_state_dict, step: the second step must read and write the LOADED moment tensors (load_state_dict
+    replaces them), exactly as torch.optim.AdamW(fused=True) does."""
+    from b200ex.optim import AdamW
+
+    dtype = torch.bfloat16
+    ours, theirs, donor = _params(dtype), _params(dtype), _params(dtype, seed=5)
+    kw = dict(lr=3e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    a, b, d = AdamW(ours, **kw), torch.optim.AdamW(theirs, fused=True, **kw), torch.optim.AdamW(donor, fused=True, **kw)
+    for step in range(3):  # a checkpoint from another run
+        _set_grads(donor, 50 + step)
+        d.step()
+    _set_grads(ours, 0), _set_grads(theirs, 0)
+    a.step(), b.step()  # warm-up step before the resume
+    sd = d.state_dict()
+    a.load_state_dict(sd), b.load_state_dict(sd)
+    for step in range(1, 3):
+        _set_grads(ours, step), _set_grads(theirs, step)
+        a.step(), b.step()
+    torch.cuda.synchronize()
+    for i, (p, q) in enumerate(zip(ours, theirs)):
+        sa, sb = a.state[p], b.state[q]
+        assert float(sa["step"]) == float(sb["step"]) == 5.0
+        for name, x, y in (("param", p.data, q.data), ("exp_avg", sa["exp_avg"], sb["exp_avg"]), ("exp_avg_sq", sa["exp_avg_sq"], sb["exp_avg_sq"])):
+            _close(x, y, dtype, f"{name} of tensor {i} after resume")
+    # and what is saved afterwards is what was updated
+    saved = a.state_dict()["state"]
+    assert all(torch.equal(saved[i]["exp_avg"], a.state[p]["exp_avg"]) for i, p in enumerate(ours))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_offset_views_are_updated_element_by_element(dtype):
+    """Contiguous parameters that do not start on a 16-byte address (a slice of a flat buffer, p[1:]) take the scalar
+    path of the kernel instead of faulting on a misaligned vector access."""
+    from b200ex.optim import AdamW
+
+    g = torch.Generator().manual_seed(11)
+    flat_a = (torch.randn(3 * 8192 + 64, generator=g) * 0.5).to(dtype).to(DEV)
+    flat_b = flat_a.clone()
+    cuts = [(1, 1000), (1001, 9194), (9195, 9195 + 8192 * 2 + 3)]
+    ours = [torch.nn.Parameter(flat_a[s:e]) for s, e in cuts]
+    theirs = [torch.nn.Parameter(flat_b[s:e].clone()) for s, e in cuts]
+    assert any(p.data_ptr() % 16 for p in ours)
+    kw = dict(lr=3e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    a, b = AdamW(ours, **kw), torch.optim.AdamW(theirs, fused=True, **kw)
+    for step in range(3):
+        gg = torch.Generator().manual_seed(70 + step)
+        gbuf = (torch.randn(flat_a.shape, generator=gg) * 0.1).to(dtype).to(DEV)
+        for (s, e), p, q in zip(cuts, ours, theirs):
+            p.grad, q.grad = gbuf[s:e], gbuf[s:e].clone()
+        a.step(), b.step()
+    torch.cuda.synchronize()
+    for i, (p, q) in enumerate(zip(ours, theirs)):
+        _close(p.data, q.data, dtype, f"offset param {i}")
+        _close(a.state[p]["exp_avg_sq"], b.state[q]["exp_avg_sq"], dtype, f"offset exp_avg_sq {i}")
+    # bytes outside the parameter views are untouched
+    assert torch.equal(flat_a[:1], flat_b[:1]) and torch.equal(flat_a[cuts[-1][1]:], flat_b[cuts[-1][1]:])

@@ -125,3 +125,55 @@ def test_full_size_properties():
     rowsum = dl.float().sum(1)
     assert rowsum.abs().max().item() < 2e-5  # |d| = 1/8119 ~ 1.2e-4; bf16 rounding noise over 128k terms
     assert torch.count_nonzero(dl[~valid]).item() == 0
+
+
+def test_full_size_against_the_oracle():
+    """BASELINE.json configs[3] at full size, bf16 logits [8192, 128256], against the oracle itself (not only through
+    properties): loss and n_valid from one oracle forward over all rows, dlogits compared in 1024-row slabs so that the
+    host-side comparison stays within a few GB."""
+    from b200ex import ops
+
+    g = torch.Generator().manual_seed(0)
+    rows, vocab, ignore = 8192, 128256, -100
+    logits = torch.randn(rows, vocab, generator=g, dtype=torch.float32).to(torch.bfloat16)
+    target = torch.randint(0, vocab, (rows,), generator=g)
+    target[::113] = ignore
+    gout = torch.tensor(1.0, dtype=torch.bfloat16)
+    dev_logits, dev_target = logits.to(DEV), target.to(DEV)
+    loss, rmax, rls, nvalid = ops.cross_entropy_fwd(dev_logits, dev_target, ignore)
+    dl = ops.cross_entropy_bwd(gout.to(DEV), dev_logits, dev_target, rmax, rls, nvalid, ignore)
+    torch.cuda.synchronize()
+    eloss, logp, envalid = O.cross_entropy_fwd(logits, target, ignore)
+    assert_parity(nvalid, envalid, what="full size n_valid (bit-exact)")
+    assert_parity(loss, eloss, what="full size loss", ulp_scale=logp.float().abs().max().reshape(()))
+    d = abs(float(gout)) / max(int(envalid), 1)
+    for r0 in range(0, rows, 1024):
+        sl = slice(r0, r0 + 1024)
+        edl = O.cross_entropy_bwd(gout, logp[sl], target[sl], envalid, ignore)
+        scale = edl.float().abs() * logp[sl].float().abs() * 2
+        valid = target[sl] != ignore
+        onehot = torch.zeros_like(edl, dtype=torch.float32)
+        onehot[valid, target[sl][valid]] = d
+        got = dl[sl].cpu()
+        assert_parity(got, edl, what=f"full size dlogits rows {r0}..{r0 + 1023}", ulp_scale=scale + onehot)
+        assert torch.count_nonzero(got[~valid]).item() == 0
+
+
+def test_out_of_range_target_traps_like_aten():
+    """A class index outside [0, vocab) that is not ignore_index is an error, as in ATen's nll_loss (device assert):
+    the kernel reports it and traps instead of scoring the row as zero.  Run in a child process: the trap poisons the
+    CUDA context."""
+    import subprocess
+    import sys
+
+    code = (
+        "import sys, torch; sys.path[:0] = %r; from b200ex import ops\n"
+        "lg = torch.randn(8, 64, device='cuda').bfloat16(); t = torch.randint(0, 64, (8,), device='cuda'); t[3] = 64\n"
+        "try:\n"
+        "    out = ops.cross_entropy_fwd(lg, t, -100); torch.cuda.synchronize(); print('NO ERROR', out[0].item())\n"
+        "except Exception as e:\n"
+        "    print('CUDA ERROR', type(e).__name__)\n"
+    ) % (sys.path[:4],)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert "CUDA ERROR" in r.stdout and "NO ERROR" not in r.stdout, (r.stdout, r.stderr[-500:])
+    assert "outside [0, 64)" in r.stdout + r.stderr

@@ -6,7 +6,7 @@ import pytest
 import torch
 import torch.nn.functional as F
 
-from parity import TOL, assert_parity
+from parity import TOL, assert_parity, assert_parity_or_closer, assert_tensor_scale_parity
 from thunder_env import fusions, import_thunder
 
 pytestmark = pytest.mark.gpu
@@ -30,6 +30,15 @@ def _both(fn, args, cot_seed=0, opts=None):
         diff = [t for t in a if isinstance(t, torch.Tensor) and t.requires_grad]
         grads = torch.autograd.grad(outs, diff, grad_outputs=cots, allow_unused=True) if diff else []
         res.append((outs, list(grads), jf))
+    # fp64 eager run of the same function: the arbiter of the reference's assert_closer protocol
+    a = [t.detach().clone().double().requires_grad_(t.requires_grad) if isinstance(t, torch.Tensor) and t.is_floating_point() else t for t in args]
+    out = fn(*a)
+    outs = list(out) if isinstance(out, (tuple, list)) else [out]
+    g = torch.Generator(device=DEV).manual_seed(cot_seed)
+    cots = [torch.randn(o.shape, generator=g, device=DEV, dtype=torch.float32).to(r.dtype).double() for o, r in zip(outs, res[0][0])]
+    diff = [t for t in a if isinstance(t, torch.Tensor) and t.requires_grad]
+    grads = torch.autograd.grad(outs, diff, grad_outputs=cots, allow_unused=True) if diff else []
+    res.append((outs, list(grads), None))
     torch.cuda.synchronize()
     return res
 
@@ -39,14 +48,16 @@ def _mk(*shape, dtype=BF, grad=True, seed=0, scale=1.0):
     return (torch.randn(*shape, generator=g) * scale).to(dtype).to(DEV).requires_grad_(grad)
 
 
-def _compare(res, what, ulp=None, grad_atol=0.0):
-    (o1, g1, _), (o2, g2, _) = res
-    for i, (a, b) in enumerate(zip(o1, o2)):
-        assert_parity(a, b, what=f"{what} out[{i}]", ulp_scale=ulp(b) if ulp else None)
-    for i, (a, b) in enumerate(zip(g1, g2)):
+def _compare(res, what):
+    """b200 against the torch executor at north_star's tolerances (bf16 rtol 1.6e-2 / atol 1e-5, fp32 rtol 1e-5 / atol
+    1e-6); an element outside them must be at least as close to the fp64 run as the torch executor's."""
+    (o1, g1, _), (o2, g2, _), (o3, g3, _) = res
+    for i, (a, b, r) in enumerate(zip(o1, o2, o3)):
+        assert_parity_or_closer(a, b, r, what=f"{what} out[{i}]")
+    for i, (a, b, r) in enumerate(zip(g1, g2, g3)):
         if a is None and b is None:
             continue
-        assert_parity(a, b, what=f"{what} grad[{i}]", ulp_scale=ulp(b) if ulp else None, atol_extra=grad_atol)
+        assert_parity_or_closer(a, b, r, what=f"{what} grad[{i}]")
 
 
 @pytest.mark.parametrize("dtype", [BF, F32])
@@ -58,8 +69,7 @@ def test_rmsnorm_residual(dtype):
     res = _both(f, [_mk(64, 512, dtype=dtype, seed=1), _mk(64, 512, dtype=dtype, seed=2), _mk(512, dtype=dtype, seed=3)])
     kinds = [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
     assert "b200_rms_norm_fwd+residual" in kinds
-    # gradients of a sum of rounded terms: one bf16 ulp of the operands' magnitude
-    _compare(res, f"rmsnorm {dtype}", ulp=(lambda b: b.float().abs() + 4.0) if dtype is BF else None, grad_atol=0 if dtype is BF else 2e-5)
+    _compare(res, f"rmsnorm {dtype}")
 
 
 @pytest.mark.parametrize("dtype", [BF, F32])
@@ -74,7 +84,7 @@ def test_layer_norm(dtype, bias):
     jf = res[0][2]
     assert "b200_layer_norm_fwd" in [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks]
     assert "b200_layer_norm_bwd" in [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks]
-    _compare(res, f"layer_norm {dtype}", ulp=lambda b: b.float().abs() * (1.0 if dtype is BF else 16.0) + 8.0, grad_atol=0 if dtype is BF else 2e-5)
+    _compare(res, f"layer_norm {dtype}")
 
 
 @pytest.mark.parametrize("dtype", [BF, F32])
@@ -88,21 +98,21 @@ def test_softmax_with_scale_and_mask(dtype):
     jf = res[0][2]
     assert "b200_softmax_fwd" in [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks]
     assert "b200_softmax_bwd" in [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks]
-    _compare(res, f"softmax {dtype}", ulp=lambda b: b.float().abs() * 4 + 1.0, grad_atol=0 if dtype is BF else 2e-5)
+    _compare(res, f"softmax {dtype}")
 
 
 def test_swiglu_inline_expression():
     res = _both(lambda a, b: F.silu(a) * b, [_mk(128, 1024, seed=4, scale=2.0), _mk(128, 1024, seed=5)])
     kinds = [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
     assert kinds, "swiglu was not claimed"
-    _compare(res, "swiglu", ulp=lambda b: b.float().abs() * 2 + 1e-2)
+    _compare(res, "swiglu")
 
 
 def test_swiglu_function_is_native():
     res = _both(lambda a, b: b200.swiglu(a, b), [_mk(64, 2048, seed=6, scale=2.0), _mk(64, 2048, seed=7)])
     fw = fusions(thunder.last_traces(res[0][2])[-1])
     assert [k for _, ks in fw for k in ks] == ["b200_swiglu"]
-    _compare(res, "b200.swiglu", ulp=lambda b: b.float().abs() * 2 + 1e-2)
+    _compare(res, "b200.swiglu")
 
 
 @pytest.mark.parametrize("dtype", [BF, F32])
@@ -116,7 +126,7 @@ def test_cross_entropy(dtype):
 
     res = _both(f, [logits, tgt])
     assert "b200_cross_entropy_fwd" in [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks]
-    _compare(res, f"cross_entropy {dtype}", ulp=(lambda b: b.float().abs() * 16 + 1e-7) if dtype is BF else None)
+    _compare(res, f"cross_entropy {dtype}")
 
 
 def test_qkv_split_rope_function():
@@ -124,7 +134,7 @@ def test_qkv_split_rope_function():
     cos, sin = _mk(64, 32, grad=False, seed=10), _mk(64, 32, grad=False, seed=11)
     res = _both(lambda q, c, s: b200.qkv_split_rope(q, c, s, 8, 2, 32, 32), [qkv, cos, sin])
     assert [k for _, ks in fusions(thunder.last_traces(res[0][2])[-1]) for k in ks] == ["b200_qkv_split_rope"]
-    _compare(res, "qkv_split_rope", grad_atol=2.0**-6)
+    _compare(res, "qkv_split_rope")
 
 
 @pytest.mark.parametrize("act", ["gelu", "relu"])
@@ -137,14 +147,14 @@ def test_bias_activation(act):
     fwd_kind, bwd_kind = (f"b200k_bias_act_fwd[{act}]", f"b200k_bias_act_bwd[{act}]") if act == "gelu" else ("b200k_pointwise", "b200k_pointwise")
     assert [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks] == [fwd_kind]
     assert [k for _, ks in fusions(thunder.last_backward_traces(jf)[-1]) for k in ks] == [bwd_kind, "b200k_colsum"]
-    _compare(res, f"bias_{act}", ulp=lambda b: b.float().abs() * 4 + 2.0)
+    _compare(res, f"bias_{act}")
 
 
 def test_tanh_chain_goes_through_the_generic_interpreter_and_colsum():
     res = _both(lambda x, b: torch.tanh(x * b) + 0.5 * x, [_mk(256, 768, seed=21), _mk(768, seed=22)])
     kinds = [k for _, ks in fusions(thunder.last_backward_traces(res[0][2])[-1]) for k in ks]
     assert "b200k_pointwise" in kinds and "b200k_colsum" in kinds
-    _compare(res, "tanh chain", ulp=lambda b: b.float().abs() * 4 + 2.0)
+    _compare(res, "tanh chain")
 
 
 def test_generic_pointwise_fp32_with_broadcasts():
@@ -153,7 +163,7 @@ def test_generic_pointwise_fp32_with_broadcasts():
         return torch.where(z > 0.1, z, 0.01 * z) * s, torch.sqrt(torch.abs(x)) + s
 
     res = _both(f, [_mk(8, 33, 65, dtype=F32, seed=14), _mk(8, 33, 65, dtype=F32, seed=15), _mk(65, dtype=F32, seed=16)])
-    _compare(res, "generic pointwise", grad_atol=1e-5)
+    _compare(res, "generic pointwise")
 
 
 def test_region_callable_is_reused_and_handles_new_strides():
@@ -197,12 +207,7 @@ def test_tiny_llama_forward_backward(fusion_type):
     assert fk.count("b200_qkv_split_rope") == cfg.n_layer and "b200_cross_entropy_fwd" in fk and "b200_cross_entropy_bwd" in bk
     assert fk.count("b200_rms_norm_fwd+residual") == 2 * cfg.n_layer
     torch.testing.assert_close(results["b200"][0].float(), results["torch"][0].float(), rtol=1.6e-2, atol=1e-5)
-    for n, g in results["b200"][1].items():
-        ref = results["torch"][1][n]
-        # parameter gradients are GEMM outputs of bf16 activations that differ by an ulp here and there: compare
-        # in the aggregate, relative to the gradient's scale
-        err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
-        assert err.item() < 2e-2, f"grad {n}: relative error {err.item():.3e}"
+    _grads_close(results)
 
 
 def test_llama3_8b_block_full_size():
@@ -231,7 +236,7 @@ def test_llama3_8b_block_full_size():
     fk = [k for _, ks in fusions(thunder.last_traces(jb)[-1]) for k in ks]
     bk = [k for _, ks in fusions(thunder.last_backward_traces(jb)[-1]) for k in ks]
     # region census of SURVEY Appendix C, all on hand-written kernels
-    assert sorted(fk) == sorted(["b200_rms_norm_fwd", "b200_qkv_split_rope", "b200_rms_norm_fwd+residual", "b200k_swiglu_fwd", "b200k_pointwise"])
+    assert sorted(fk) == sorted(["b200_rms_norm_fwd", "b200_qkv_split_rope", "b200_rms_norm_fwd+residual", "b200k_swiglu_fwd", "b200k_pointwise"]), fk
     assert "b200k_swiglu_bwd" in bk and "b200_qkv_rope_bwd" in bk and bk.count("b200_rms_norm_bwd") + bk.count("b200_rms_norm_bwd+residual") == 2
 
     def rel(a, b):
@@ -239,9 +244,12 @@ def test_llama3_8b_block_full_size():
 
     # outputs of GEMM/attention chains over bf16 activations that differ by an ulp here and there: aggregate error
     assert rel(res["b200"][0], res["torch"][0]) < 1e-2
-    assert rel(res["b200"][1], res["torch"][1]) < 2e-2
+    assert rel(res["b200"][1], res["torch"][1]) < 1.6e-2
+    assert_tensor_scale_parity(res["b200"][0], res["torch"][0], what="block output")
+    assert_tensor_scale_parity(res["b200"][1], res["torch"][1], what="block input gradient")
     for n, g in res["b200"][2].items():
-        assert rel(g, res["torch"][2][n]) < 2e-2, f"grad {n}"
+        assert rel(g, res["torch"][2][n]) < 1.6e-2, f"grad {n}"
+        assert_tensor_scale_parity(g, res["torch"][2][n], what=f"grad {n}")
 
 
 class _Gpt2Block(torch.nn.Module):
@@ -304,10 +312,7 @@ def test_tiny_gpt2_forward_backward():
     assert fk.count("b200_layer_norm_fwd") == 5 and bk.count("b200_layer_norm_bwd") == 5
     assert fk.count("b200_softmax_fwd") == 2 and bk.count("b200_softmax_bwd") == 2
     torch.testing.assert_close(results["b200"][0].float(), results["torch"][0].float(), rtol=1.6e-2, atol=1e-5)
-    for n, g in results["b200"][1].items():
-        ref = results["torch"][1][n]
-        err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
-        assert err.item() < 2e-2, f"grad {n}: relative error {err.item():.3e}"
+    _grads_close(results)
 
 
 def test_readme_mlp_fp32_on_the_gpu():
@@ -329,11 +334,14 @@ def test_readme_mlp_fp32_on_the_gpu():
         torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
 
 
-def _grads_close(results, tol=2e-2):
+def _grads_close(results, tol=1.6e-2):
+    """Parameter gradients: elementwise at rtol 1.6e-2 plus one bf16 ulp of the gradient tensor's largest magnitude (one
+    differently rounded term of the sums they are), and norm-wise within rtol."""
     for n, g in results["b200"][1].items():
         ref = results["torch"][1][n]
         err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
         assert err.item() < tol, f"grad {n}: relative error {err.item():.3e}"
+        assert_tensor_scale_parity(g, ref, what=f"grad {n}")
 
 
 def test_reference_llama2_model():
