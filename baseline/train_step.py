@@ -52,7 +52,10 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
 
         dist.init_process_group("nccl", device_id=device)
         own_pg = True
-    cfg = LlamaConfig(n_layer=args.layers)
+    # "litgpt": RMSNorm and the attention slice spelled with plain torch ops as litgpt does (b200 finds the regions
+    # itself); "ops": F.rms_norm + b200ex.executor.qkv_split_rope (op-level route to the hand-written kernels)
+    spelling = os.environ.get("B200_MODEL_SPELLING", getattr(args, "spelling", "litgpt"))
+    cfg = LlamaConfig(n_layer=args.layers, spelling=spelling)
     B, T = args.micro_batch, args.seq_len
     torch.manual_seed(1234)
     t0 = time.perf_counter()
@@ -146,7 +149,7 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
             "metric": "llama3_8b_train_tokens_per_s", "value": tokens_per_s, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"llama_step: LitGPT-style Llama-3-8B shape, n_layer={cfg.n_layer}, micro-batch {B} x seq {T} per GPU, {optimizer_name}, attention: {attention_name}, "
+            "config": {"workload": f"llama_step: LitGPT-style Llama-3-8B shape ({cfg.spelling} spelling), n_layer={cfg.n_layer}, micro-batch {B} x seq {T} per GPU, {optimizer_name}, attention: {attention_name}, "
                                    f"{'fsdp ZeRO-2 (thunder.distributed.fsdp, NCCL)' if world > 1 else 'single GPU'}",
                        "executors": [str(e) if isinstance(e, str) else e.name for e in execs], "fusion_type": args.fusion_type,
                        "params": n_params},

@@ -92,12 +92,39 @@ class Workload:
         return [(self.name + " fwd", lambda i: self.fwd(self.sets[i % NSETS]), self.fwd_bytes),
                 (self.name + " bwd", lambda i: self.bwd(self.sets[i % NSETS], self.saved[i % NSETS]), self.bwd_bytes)]
 
-    def e2e_out_host(self):
-        f = self.saved[0]
-        b = self.bwd(self.sets[0], f)
+    # ---- end to end through the plugin boundary: thunder.jit(fn, executors=[b200]) ---------------------------------
+    def jit_setup(self, thunder, b200):
+        """The workload's defining PyTorch function (reference_fn) compiled by the reference with the b200 executor:
+        the call a user of the reference makes.  Forward = the jitted callable, backward = autograd through it."""
+        fn, self._diff, self._cot = self.reference_fn()
+        self._jf = thunder.jit(fn, executors=[b200.ex])
+
+    def jit_fwd(self, d):
+        args = [d[k].requires_grad_(True) if (k in self._diff and d[k].is_floating_point()) else d[k] for k in self.fwd_inputs]
+        outs = self._jf(*args)
+        outs = list(outs) if isinstance(outs, (tuple, list)) else [outs]
+        f = {f"out{i}": o for i, o in enumerate(outs)}
+        f["_args"] = args
+        return f
+
+    def jit_bwd(self, d, f):
+        outs = [f[k] for k in sorted(k for k in f if k.startswith("out"))]
+        dargs = [a for a in f["_args"] if a.requires_grad]
+        grads = torch.autograd.grad(outs, dargs, grad_outputs=[d[k] for k in self._cot])
+        return {f"grad{i}": g for i, g in enumerate(grads)}
+
+    def e2e_out_host(self, use_jit=False):
+        if use_jit:
+            d = {k: v.detach().clone() for k, v in self.sets[0].items()}
+            f = self.jit_fwd(d)
+            b = self.jit_bwd(d, f)
+            f = {k: v.detach() for k, v in f.items() if k != "_args"}
+        else:
+            f = self.saved[0]
+            b = self.bwd(self.sets[0], f)
         return {k: torch.empty(v.shape, dtype=v.dtype).pin_memory() for k, v in {**f, **b}.items()}
 
-    def e2e_run(self, host, device, out_host, steps: int, stream):
+    def e2e_run(self, host, device, out_host, steps: int, stream, use_jit=False):
         """`steps` steps from pinned host buffers.  Every step copies its inputs host -> device, launches forward and
         backward, copies every result device -> host and waits for them (the caller reads the step's results on the
         host).  Three streams: a copy-in stream runs one step ahead of the compute stream, a copy-out stream drains
@@ -106,6 +133,7 @@ class Workload:
             self._h2d, self._d2h = torch.cuda.Stream(device), torch.cuda.Stream(device)
         h2d, d2h = self._h2d, self._d2h
         bwd_only = [k for k in host if k not in self.fwd_inputs]
+        fwd_fn, bwd_fn = (self.jit_fwd, self.jit_bwd) if use_jit else (self.fwd, self.bwd)
 
         def load(keys):
             with torch.cuda.stream(h2d):
@@ -120,7 +148,8 @@ class Workload:
             d2h.wait_event(ev)
             with torch.cuda.stream(d2h):
                 for k, v in res.items():
-                    out_host[k].copy_(v, non_blocking=True)
+                    if k in out_host:
+                        out_host[k].copy_(v.detach(), non_blocking=True)
 
         h2d.wait_stream(stream)
         nxt = load(self.fwd_inputs)
@@ -130,11 +159,11 @@ class Workload:
             if i + 1 < steps:
                 nxt = load(self.fwd_inputs)  # next step's inputs queue up behind this step's
             stream.wait_event(ev_f)
-            f = self.fwd(d)
+            f = fwd_fn(d)
             drain(f)
             stream.wait_event(ev_b)
             d.update(late)
-            b = self.bwd(d, f)
+            b = bwd_fn(d, f)
             drain(b)
             d2h.synchronize()  # this step's results are on the host
         stream.wait_stream(d2h)
@@ -651,7 +680,9 @@ def run_reference_arm(args, wl):
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic", "config": {"workload": full_desc, "device": "host CPU", "executor": "thunder.jit(executors=['torch'])" if kind == "reference" else "oracle port"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": kind,
-                         "sample": f"{sample}; {args.steps} steps after {max(1, args.warmup)} warm-up, rank 0 only"},
+                         "sample": f"{sample}; {args.steps} steps after {max(1, args.warmup)} warm-up, rank 0 only",
+                         "note": "whole-box CPU figure: one process on ALL host cores (the cores do not multiply with --gpus); "
+                                 "compare per-GPU numbers with it at N=1, the N>1 ratio is N GPUs against the same host"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -698,6 +729,9 @@ def main():
     ap.add_argument("--seq-len", type=int, default=4096)
     ap.add_argument("--executor", default="b200", choices=["b200", "torch"])
     ap.add_argument("--fusion-type", default="dataflow", choices=["dataflow", "consecutive"])
+    ap.add_argument("--spelling", default="litgpt", choices=["litgpt", "ops"],
+                    help="llama_step model source: 'litgpt' = norms and the attention slice written with plain torch ops as litgpt writes them "
+                         "(b200 claims the regions itself), 'ops' = F.rms_norm + b200ex.executor.qkv_split_rope (op-level kernels)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train-step", action="store_true", help="skip the Llama-3-8B-shape training step that the default run appends as `train_step`")
     ap.add_argument("--no-e2e", action="store_true")
@@ -834,23 +868,41 @@ def main():
     # ---- end to end with host buffers ---------------------------------------------------------
     e2e = None
     if not args.no_e2e:
+        # through the reference-facing plugin call: thunder.jit(fn, executors=[b200]) on host (pinned) buffers
+        thunder = import_reference()
+        if thunder is None:
+            raise SystemExit("bench.py: baseline/_ref (the reference) is missing; run __graft_entry__.build() in the build container")
+        import b200ex.executor as b200
+
+        wl.jit_setup(thunder, b200)
         host = wl.host_inputs(99 + rank, pin=True)
-        out_host = wl.e2e_out_host()
+        out_host = wl.e2e_out_host(use_jit=True)
+        d2h_bytes = _nbytes(*out_host.values())
         e2e_steps = max(3, min(args.steps, 20))
-        wl.e2e_run(host, device, out_host, 2, stream)
+        wl.e2e_run(host, device, out_host, 2, stream, use_jit=True)
         barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
-        wl.e2e_run(host, device, out_host, e2e_steps, stream)
+        wl.e2e_run(host, device, out_host, e2e_steps, stream, use_jit=True)
         b.record(stream)
         barrier()
         ems = torch.tensor([a.elapsed_time(b)], device=device, dtype=torch.float64)
         if dist is not None:
             dist.all_reduce(ems, op=dist.ReduceOp.MAX)
+        census = {}
+        try:
+            from baseline.train_step import region_census
+
+            census = region_census(thunder, wl._jf)
+        except Exception:
+            pass
         e2e = {"value": world * wl.bytes_per_step * e2e_steps / (ems.item() / 1e3) / 1e9, "unit": UNIT,
-               "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": wl.d2h_bytes,
-               "ms_per_step": ems.item() / e2e_steps, "steps": e2e_steps,
-               "api": "b200ex.ops launchers on pinned host tensors (H2D + launch + D2H of every result per step; copy-in one step ahead, copy-out behind)"}
+               "h2d_bytes_per_step": wl.h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+               "ms_per_step": ems.item() / e2e_steps, "steps": e2e_steps, "b200_launch_kinds": census,
+               "api": "thunder.jit(fn, executors=[b200]) forward + torch.autograd.grad backward on pinned host tensors (H2D of every input, "
+                      "D2H of every output and gradient per step; copy-in one step ahead, copy-out behind)",
+               "note": "PCIe-bound: the step moves h2d + d2h bytes over the host link for a region that takes ~0.1 ms on the device; at N > 1 all ranks "
+                       "share one host's memory and PCIe root, so this column does not scale with N"}
 
     sampler.mark_load(False)
     clocks = sampler.stop() if rank == 0 else None
@@ -868,7 +920,7 @@ def main():
             from baseline import train_step
 
             targs = argparse.Namespace(layers=args.layers, micro_batch=args.micro_batch, seq_len=args.seq_len, executor="b200",
-                                       fusion_type=args.fusion_type, steps=5, warmup=3)
+                                       fusion_type=args.fusion_type, steps=5, warmup=3, spelling=args.spelling)
             train = train_step.run(targs, thunder, ClockSampler, dist=dist, emit=False)
         except Exception as e:  # the region metric above must still be reported
             train = {"error": f"{type(e).__name__}: {e}"[:500]}

@@ -261,6 +261,57 @@ class B200Executor(FusionExecutor):
                 runs.append(([b], f))
         return [(r, f and not all(_all_tagged(b, prims.OpTags.SHAPE_OP) for b in r)) for r, f in runs]
 
+    # -- trace-level common-subexpression elimination (nvfuserex_impl.py:743-833) ------------
+    def cse(self, trace: TraceCtx) -> TraceCtx:
+        """One pass over the fused trace with the reference's own per-symbol helper (``cse_single_bsym``):
+
+        * outside fusions, a bound symbol whose right-hand side already occurred is dropped and its outputs are
+          renamed to the earlier ones;
+        * inside a fusion the same is done over its subsymbols (after rematerialisation two regions often carry the
+          same recomputed producer chain, and one region can carry it twice), with renamings from earlier regions
+          applied only to proxies that still are arguments of this one;
+        * a fusion's arguments and outputs that became the same value are passed / returned once.
+
+        ``update_fusion_call_ctx`` afterwards rebuilds every fusion callable from its new subsymbols."""
+        from dataclasses import replace as dc_replace
+
+        from thunder.core.pytree import tree_map
+        from thunder.core.transform_common import cse_single_bsym, replace_redundant_inputs
+
+        start = time.perf_counter_ns()
+        out = from_trace(trace)
+        seen_outside: dict = {}
+        renamed: dict[Variable, Proxy] = {}
+        rename = lambda x: renamed.get(Variable(x), x) if isinstance(x, Proxy) else x
+        uniq = lambda xs: tuple({variableify(x) if isinstance(x, Proxy) else id(x): x for x in xs}.values())
+        new: list[BoundSymbol] = []
+        for bsym in trace.bound_symbols:
+            if not bsym.sym.is_fusion:
+                b = cse_single_bsym(renamed, seen_outside, bsym)
+                if b is not None:
+                    new.append(b)
+                continue
+            args_v = {variableify(a) for a in bsym.flat_proxy_args}
+            local = {k: v for k, v in renamed.items() if k in args_v}
+            seen_inside: dict = {}
+            subs = [b for b in (cse_single_bsym(local, seen_inside, s) for s in bsym.subsymbols) if b is not None]
+            subs = replace_redundant_inputs(local, subs)
+            renamed.update(local)
+            args = tree_map(rename, bsym.args)
+            outs = tree_map(rename, bsym.output)
+            if isinstance(args, (tuple, list)):
+                args = uniq(args)
+            if isinstance(outs, (tuple, list)):
+                outs = uniq(outs)
+            new.append(dc_replace(bsym, args=args, subsymbols=tuple(subs), output=outs))
+        ret = new[-1]
+        utils.check(ret.sym.id == PrimIDs.RETURN, lambda: "b200 cse: the trace does not end in a return", exception_type=AssertionError)
+        new[-1] = prims.python_return.bind(*tree_map(rename, ret.args), output=None)
+        out.bound_symbols = new
+        ms = (time.perf_counter_ns() - start) // 1000000
+        out.set_provenance(TraceProvenance(f"b200 common subexpression elimination (took {ms} milliseconds)"))
+        return out
+
     # -- the pass (nvfuserex_impl.py:836-939) ---------------------------------------------------------
     def fusion_pass(self, trace: TraceCtx) -> TraceCtx:
         start = time.perf_counter_ns()
@@ -338,11 +389,11 @@ class B200Executor(FusionExecutor):
         done = None
         if self._use_rematerialization:
             try:
-                done = update_fusion_call_ctx(dce(rematerialize(fusedtrace)))
+                done = update_fusion_call_ctx(dce(self.cse(rematerialize(fusedtrace))))
             except PwUnsupported as e:
                 if os.environ.get("B200EX_DEBUG"):
                     print(f"[b200ex] regions kept as partitioned, a rematerialised one did not lower: {e}", flush=True)
-        fusedtrace = done if done is not None else update_fusion_call_ctx(dce(fusedtrace))
+        fusedtrace = done if done is not None else update_fusion_call_ctx(dce(self.cse(fusedtrace)))
         ms = (time.perf_counter_ns() - start) // 1000000
         fusedtrace.set_provenance(TraceProvenance(f"b200 fusion (took {ms} milliseconds)"))
         return fusedtrace

@@ -1135,7 +1135,7 @@ def _fold(P: Program, assume: dict):
 MAX_BLOCKS = 48
 
 
-def generate_flat(P: Program, modes: tuple, unroll: int) -> str:
+def generate_flat(P: Program, modes: tuple, unroll: int, min_ctas: int = 0) -> str:
     """Flat (gather) kernel.  Conditions are uniform over a work item, so `cat` / `pad` selections become control
     flow: the program is specialised per reachable combination of conditions and every specialisation loads only
     the leaves it needs (register pressure is the widest branch, not the sum of all pieces)."""
@@ -1147,7 +1147,8 @@ def generate_flat(P: Program, modes: tuple, unroll: int) -> str:
     it = "u32" if math.prod(ext) < 2**31 else "i64"
     _, _, und0 = _fold(P, {})
     U = unroll
-    L.append('extern "C" __global__ void __launch_bounds__(256) rk_main(const __grid_constant__ Params P) {')
+    bounds = f"256, {min_ctas}" if min_ctas else "256"
+    L.append(f'extern "C" __global__ void __launch_bounds__({bounds}) rk_main(const __grid_constant__ Params P) {{')
     L.append(f"  const {it} TOTAL = {total};")
     L.append(f"  for ({it} base = ({it})blockIdx.x * {256 * U} + threadIdx.x; base < TOTAL; base += ({it})gridDim.x * {256 * U}) {{")
     L.append(f"    {it} x[{U}][{max(nv, 1)}]; bool live[{U}];")
@@ -1586,6 +1587,14 @@ class _Kernel:
         self.launches = 0
         self._occ: dict = {}
 
+    def local_bytes(self) -> int:
+        """Per-thread local memory of rk_main: non-zero means the register cap made it spill."""
+        try:
+            (n,) = jit._check(self.driver.cuFuncGetAttribute(self.driver.CUfunction_attribute.CU_FUNC_ATTRIBUTE_LOCAL_SIZE_BYTES, self.main), "cuFuncGetAttribute")
+            return int(n)
+        except Exception:
+            return 1
+
     def ctas_per_sm(self, block: int) -> int:
         """Resident CTAs per SM for `rk_main` at this block size.  Persistent grids are sized with it: a grid that is
         not a whole number of resident waves leaves part of the GPU idle for the last one."""
@@ -1614,8 +1623,8 @@ def flat_unroll(P: Program) -> int:
     return 4 if n <= 2 else (2 if n <= 5 else 1)
 
 
-def source_for(P: Program, modes: tuple) -> str:
-    return generate_flat(P, modes, flat_unroll(P)) if P.kind == "flat" else generate_row(P, modes)
+def source_for(P: Program, modes: tuple, min_ctas: int = 0) -> str:
+    return generate_flat(P, modes, flat_unroll(P), min_ctas) if P.kind == "flat" else generate_row(P, modes)
 
 
 def _get_kernel(P: Program, modes: tuple, dev_index: int) -> _Kernel:
@@ -1625,9 +1634,18 @@ def _get_kernel(P: Program, modes: tuple, dev_index: int) -> _Kernel:
         with _klock:
             k = _kernels.get(key)
             if k is None:
-                src = source_for(P, modes)
                 with torch.cuda.device(dev_index):
-                    k = _Kernel(jit.compile_cubin(src), any(o.kind == "col" for o in P.outputs))
+                    k = None
+                    if P.kind == "flat" and P.conds:
+                        # Branchy gather kernels are issue-bound and short on registers by a few: ask for full
+                        # occupancy (8 then 6 CTAs of 256 threads per SM) and keep the first build that does not spill.
+                        for want in (8, 6, 5):
+                            cand = _Kernel(jit.compile_cubin(source_for(P, modes, want)), False)
+                            if cand.local_bytes() == 0:
+                                k = cand
+                                break
+                    if k is None:
+                        k = _Kernel(jit.compile_cubin(source_for(P, modes)), any(o.kind == "col" for o in P.outputs))
                 _kernels[key] = k
     return k
 

@@ -98,8 +98,11 @@ def test_load_state_dict_after_a_step_switches_to_the_loaded_moments():
         d.step()
     _set_grads(ours, 0), _set_grads(theirs, 0)
     a.step(), b.step()  # warm-up step before the resume
+    import copy
+
     sd = d.state_dict()
-    a.load_state_dict(sd), b.load_state_dict(sd)
+    # load_state_dict keeps tensors that already have the right device / dtype: each optimizer gets its own copy
+    a.load_state_dict(copy.deepcopy(sd)), b.load_state_dict(copy.deepcopy(sd))
     for step in range(1, 3):
         _set_grads(ours, step), _set_grads(theirs, step)
         a.step(), b.step()

@@ -194,7 +194,7 @@ def test_llama_block_region_census():
     named family is lowered to its hand-written kernel."""
     from baseline.llama_model import GPT, build_rope_cache, tiny_config
 
-    cfg = tiny_config()
+    cfg = tiny_config(spelling="ops")
     torch.manual_seed(0)
     m = GPT(cfg).to(torch.bfloat16)
     cos, sin = build_rope_cache(16, cfg.rope_n_elem, dtype=torch.bfloat16)
@@ -256,3 +256,49 @@ def test_signature_table_is_current():
         b200._NATIVE_SIGNATURES.clear()
         b200._NATIVE_SIGNATURES.update(committed)
     assert table == committed and len(table) >= 4
+
+
+def test_trace_level_cse_removes_duplicate_subsymbols():
+    """thunder/tests/test_nvfuser.py:190-215: (t0 + 5) is computed twice in the source, once in the fused trace."""
+    b200._testing_claim_cpu(True)
+    try:
+        def func(x):
+            t0 = x.relu()
+            t1 = t0 + 5
+            t2 = t0 + 5
+            t3 = t0 @ t0
+            return torch.where(t3 > t1, t1, t2)
+
+        jf = thunder.jit(func, executors=[b200.ex])
+        with pytest.raises(RuntimeError, match="CUDA"):
+            jf(torch.randn(5, 5))
+        tr = thunder.last_traces(jf)[-1]
+        fs = [b for b in tr.bound_symbols if b.sym.is_fusion]
+        assert len(fs) == 2  # split by the matmul
+        adds = [s for f in fs for s in f.subsymbols if s.sym.name == "add"]
+        assert len(adds) == 1, [s.sym.name for f in fs for s in f.subsymbols]
+    finally:
+        b200._testing_claim_cpu(False)
+
+
+def test_trace_level_cse_dedupes_fusion_arguments():
+    """thunder/tests/test_nvfuser.py:218-245: x @ y appears twice; after CSE the single fusion takes one matmul result
+    plus z and w, and returns one tensor."""
+    b200._testing_claim_cpu(True)
+    try:
+        def func(w, x, y, z):
+            t1 = (x @ y) + z
+            t3 = (x @ y) + w
+            return t1 + t3
+
+        jf = thunder.jit(func, executors=[b200.ex], fusion_type="dataflow")
+        with pytest.raises(RuntimeError, match="CUDA"):
+            jf(*[torch.randn(5, 5) for _ in range(4)])
+        tr = thunder.last_traces(jf)[-1]
+        fs = [b for b in tr.bound_symbols if b.sym.is_fusion]
+        assert len(fs) == 1
+        assert len([b for b in tr.bound_symbols if b.sym.name == "matmul"]) == 1
+        assert len(fs[0].flat_proxy_args) == 3 and {a.name for a in fs[0].flat_proxy_args} >= {"z", "w"}
+        assert len(fs[0].flat_proxy_outs) == 1
+    finally:
+        b200._testing_claim_cpu(False)

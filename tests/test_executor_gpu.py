@@ -185,7 +185,7 @@ def test_tiny_llama_forward_backward(fusion_type):
     from baseline.llama_model import GPT, build_rope_cache, tiny_config
     from thunder.executors.sdpaex import sdpa_ex
 
-    cfg = tiny_config(n_embd=128, intermediate_size=256, n_head=4, n_query_groups=2, padded_vocab_size=512)
+    cfg = tiny_config(spelling="ops", n_embd=128, intermediate_size=256, n_head=4, n_query_groups=2, padded_vocab_size=512)
     torch.manual_seed(0)
     model = GPT(cfg).to(DEV).to(BF)
     B, T = 2, 64
@@ -216,7 +216,9 @@ def test_llama3_8b_block_full_size():
     from baseline.llama_model import LLAMA3_8B, Block, build_rope_cache
     from thunder.executors.sdpaex import sdpa_ex
 
-    cfg = LLAMA3_8B
+    import dataclasses
+
+    cfg = dataclasses.replace(LLAMA3_8B, spelling="ops")  # the op-level route; the litgpt spelling is tests/test_regionc_gpu.py
     torch.manual_seed(0)
     block = Block(cfg).to(DEV).to(BF)
     B, T = 2, 4096
@@ -339,7 +341,10 @@ def _grads_close(results, tol=1.6e-2):
     differently rounded term of the sums they are), and norm-wise within rtol."""
     for n, g in results["b200"][1].items():
         ref = results["torch"][1][n]
-        err = (g.float() - ref.float()).norm() / (ref.float().norm() + 1e-12)
+        # norm-wise, with one bf16 ulp of the tensor's scale on every element as the floor (a gradient that is zero
+        # in exact arithmetic — a key-projection bias under softmax — is rounding noise in both runs)
+        floor = 2.0**-8 * ref.float().abs().max() * ref.numel() ** 0.5
+        err = (g.float() - ref.float()).norm() / (ref.float().norm() + floor + 1e-12)
         assert err.item() < tol, f"grad {n}: relative error {err.item():.3e}"
         assert_tensor_scale_parity(g, ref, what=f"grad {n}")
 

@@ -195,3 +195,46 @@ def test_output_views_cost_no_kernel():
     want = fn(x, y)
     for a, b in zip((z, z2, z2t), want):
         assert torch.equal(a, b)
+
+
+def test_llama3_8b_block_in_litgpt_spelling_full_size():
+    """BASELINE.json configs[2] with the model written as litgpt writes it (inline RMSNorm, plain-ops QKV split + RoPE;
+    nothing in it names this repository): b200 finds the regions itself — row kernels for the norms, one gather kernel
+    each way for the attention slice, the native SwiGLU kernels — and agrees with the torch executor."""
+    import dataclasses
+
+    from baseline.llama_model import LLAMA3_8B, Block, build_rope_cache
+    from parity import assert_tensor_scale_parity
+    from thunder.executors.sdpaex import sdpa_ex
+
+    cfg = dataclasses.replace(LLAMA3_8B, spelling="litgpt")
+    torch.manual_seed(0)
+    block = Block(cfg).to(DEV).to(BF)
+    B, T = 2, 4096
+    cos, sin = build_rope_cache(T, cfg.rope_n_elem, base=cfg.rope_base, device=DEV, dtype=BF)
+    x0 = (torch.randn(B, T, cfg.n_embd, device=DEV) * 0.5).to(BF)
+    cot = torch.randn(B, T, cfg.n_embd, device=DEV).to(BF)
+    res = {}
+    for name, execs in (("b200", [sdpa_ex, b200.ex]), ("torch", [sdpa_ex, "torch"])):
+        block.zero_grad(set_to_none=True)
+        x = x0.clone().requires_grad_(True)
+        jb = thunder.jit(block, executors=execs)
+        y = jb(x, cos, sin)
+        y.backward(cot)
+        res[name] = (y.detach(), x.grad.detach(), {n: p.grad.detach().clone() for n, p in block.named_parameters()}, jb)
+    torch.cuda.synchronize()
+    jb = res["b200"][3]
+    fk = [k for _, ks in fusions(thunder.last_traces(jb)[-1]) for k in ks]
+    bk = [k for _, ks in fusions(thunder.last_backward_traces(jb)[-1]) for k in ks]
+    assert fk.count("b200k_region[row]") == 2 and fk.count("b200k_region[gather]") == 1 and "b200k_swiglu_fwd" in fk, fk
+    assert bk.count("b200k_region[row]") == 2 and bk.count("b200k_region[gather]") == 1 and "b200k_swiglu_bwd" in bk, bk
+
+    def rel(a, b):
+        return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
+
+    assert rel(res["b200"][0], res["torch"][0]) < 1e-2 and rel(res["b200"][1], res["torch"][1]) < 1.6e-2
+    assert_tensor_scale_parity(res["b200"][0], res["torch"][0], what="block output")
+    assert_tensor_scale_parity(res["b200"][1], res["torch"][1], what="block input gradient")
+    for n, g in res["b200"][2].items():
+        assert rel(g, res["torch"][2][n]) < 1.6e-2, f"grad {n}"
+        assert_tensor_scale_parity(g, res["torch"][2][n], what=f"grad {n}")
