@@ -221,6 +221,33 @@ def compile_cubin(source: str) -> bytes:
     return cubin
 
 
+_culaunch = {"fn": None, "tried": False}
+
+
+def fast_launch(driver, func, grid: int, block: int, stream: int, params_addr: int) -> None:
+    """cuLaunchKernel(func, grid, 1, 1, block, 1, 1, 0, stream, {&params}, 0).  Goes straight to libcuda through
+    ctypes — a couple of microseconds — and only falls back to the cuda-python wrapper (ten times that per call, which
+    is as long as some of the kernels) when libcuda cannot be opened that way."""
+    if not _culaunch["tried"]:
+        _culaunch["tried"] = True
+        try:
+            lib = ctypes.CDLL("libcuda.so.1")
+            fn = lib.cuLaunchKernel
+            fn.restype = ctypes.c_int
+            fn.argtypes = [ctypes.c_void_p] + [ctypes.c_uint] * 7 + [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+            _culaunch["fn"] = fn
+        except Exception:
+            _culaunch["fn"] = None
+    argv = (ctypes.c_void_p * 1)(params_addr)
+    fn = _culaunch["fn"]
+    if fn is not None:
+        err = fn(int(func), grid, 1, 1, block, 1, 1, 0, stream, ctypes.addressof(argv), None)
+    else:
+        (err,) = driver.cuLaunchKernel(func, grid, 1, 1, block, 1, 1, 0, stream, ctypes.addressof(argv), 0)
+    if int(err) != 0:
+        raise RuntimeError(f"b200ex jit: cuLaunchKernel failed: {err}")
+
+
 class JitKernel:
     """One specialised kernel, loaded on one device."""
 
@@ -237,10 +264,7 @@ class JitKernel:
         per_cta = 256 * self.unroll
         want = (total_items + per_cta - 1) // per_cta
         grid = max(1, min(want, sm_count * 8))
-        argv = (ctypes.c_void_p * 1)(ctypes.addressof(params))
-        (err,) = self._driver.cuLaunchKernel(self.func, grid, 1, 1, 256, 1, 1, 0, stream, ctypes.addressof(argv), 0)
-        if int(err) != 0:
-            raise RuntimeError(f"b200ex jit: cuLaunchKernel failed: {err}")
+        fast_launch(self._driver, self.func, grid, 256, stream, ctypes.addressof(params))
         self.launches += 1
 
 

@@ -451,6 +451,7 @@ class PwLaunch:
     MAX_PLANS = 2048
     use_small_form = True  # tests flip this to compare the register-resident and the generic interpreter
     use_jit = True         # False: always interpret (b200k_pointwise), never specialise with NVRTC
+    force_interpreter = False  # tests: keep non-vectorisable launches on the interpreter instead of the gather kernel
     jit_failures: list = []
 
     def __init__(self, spec: PwProgramSpec, gen_info: dict | None = None):
@@ -463,6 +464,8 @@ class PwLaunch:
         self.plan_hits = 0
         self.plan_misses = 0
         self.jit_launches = 0
+        self.gather_launches = 0
+        self._gather = None
 
     @staticmethod
     def _leaf_strides(t: torch.Tensor, mapping, ndim):
@@ -593,6 +596,16 @@ class PwLaunch:
             self.plan_hits += 1
         if in_kernel and (plan.jit is None or plan.contig_fix):
             return self.run(env, _in_kernel_rng=False)  # this descriptor is not served by a specialised kernel
+        if plan.jit is None and not in_kernel and jit.enabled() and self.use_jit and not self.force_interpreter:
+            # not vectorisable by the skeleton above (inner extent, strides, alignment): the region compiler's gather
+            # kernel reads such operands with narrower or element-wise loads; the interpreter below is only for hosts
+            # without NVRTC
+            if self._gather is None:
+                from . import regionc
+
+                self._gather = regionc.RegionLaunch(regionc.Launch(regionc.program_from_pointwise(spec), {}))
+            self.gather_launches += 1
+            return self._gather.run({name: t for (name, _), t in zip(spec.leaves, tensors)})
         if plan.contig_fix:
             nd = len(shape)
             fixed = []

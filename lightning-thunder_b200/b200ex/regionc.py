@@ -1607,10 +1607,7 @@ class _Kernel:
         return self._occ[block]
 
     def launch(self, func, params, grid, block, stream):
-        argv = (ctypes.c_void_p * 1)(ctypes.addressof(params))
-        (err,) = self.driver.cuLaunchKernel(func, grid, 1, 1, block, 1, 1, 0, stream, ctypes.addressof(argv), 0)
-        if int(err) != 0:
-            raise RuntimeError(f"b200ex regionc: cuLaunchKernel failed: {err}")
+        jit.fast_launch(self.driver, func, grid, block, stream, ctypes.addressof(params))
         self.launches += 1
 
 
@@ -1650,6 +1647,29 @@ def _get_kernel(P: Program, modes: tuple, dev_index: int) -> _Kernel:
     return k
 
 
+def program_from_pointwise(spec) -> Program:
+    """A b200ex.pointwise program (purely elementwise, leaves mapped onto the iteration dims) as a flat region program.
+    PwLaunch uses it for launches its own vector skeleton cannot serve — inner extents that are not a multiple of 8,
+    odd strides, misaligned views — which the gather kernel reads with narrower or element-wise loads instead of
+    handing them to the ahead-of-time interpreter."""
+    ext = [int(n) for n in spec.iter_shape]
+    var = lambda d: _aff([(d, 1)])
+    leaves, in_shapes = [], {}
+    for (name, mapping), dt in zip(spec.leaves, spec.leaf_dtypes):
+        leaves.append(Leaf(name, dt, tuple(var(d) for d in mapping), ()))
+    ssa = [tuple(e) for e in spec.ssa]
+    outputs = [Out(name, dt, tuple(ext), sid, "full") for (name, dt, _), sid in zip(spec.outputs, spec.out_ids)]
+    P = Program("flat", ext, len(ext), leaves, [], ssa, outputs)
+    P.W = 1
+    if ext:
+        P.W = 8
+        while P.W > 1 and ext[-1] % P.W:
+            P.W //= 2
+    P.order = _thread_order(P)
+    P.signature = "pw:" + spec.signature + ":" + ",".join(map(str, ext))
+    return P
+
+
 class RegionLaunch:
     """One generated kernel bound to a region: ``run(env)`` reads the input tensors by name and returns
     {output name: new tensor}.  Plans (leaf access modes, parameter block) are cached per runtime descriptor of the
@@ -1686,45 +1706,43 @@ class RegionLaunch:
             result[name] = outs[src].view(shape)
         if any(0 in o.shape for o in P.outputs) or 0 in P.ext:
             return result
-        key = tuple((t.shape, t.stride(), t.dtype, t.data_ptr() % 16) for t in tensors)
+        key = tuple((t.stride(), t.dtype, t.data_ptr() & 15) for t in tensors)
         plan = self._plans.get(key)
         if plan is None:
             for t, name in zip(tensors, self.in_names):
                 if t.dim() > MAX_RANK:
                     raise RuntimeError(f"b200ex region: operand {name} has rank {t.dim()} > {MAX_RANK}")
+                if P.in_shapes is not None and tuple(t.shape) != tuple(P.in_shapes[name]):
+                    raise RuntimeError(f"b200ex region: operand {name} has shape {tuple(t.shape)}, the region was traced for {P.in_shapes[name]}")
             modes = leaf_modes(P, [tensors[s] for s in self.slot])
             kernel = _get_kernel(P, modes, dev.index)
             prm = self.Params()
-            for k, t in enumerate(tensors):
-                for i in range(t.dim()):
-                    prm.inp[k].st[i] = t.stride(i) if t.shape[i] != 1 else 0
-            plan = (kernel, prm, threading.Lock())
-            if len(self._plans) < self.MAX_PLANS:
-                self._plans[key] = plan
-        kernel, prm, lock = plan
-        sms = _sm_count()
-        stream = torch.cuda.current_stream(dev).cuda_stream
-        with lock, _on(dev):
-            for k, t in enumerate(tensors):
-                prm.inp[k].ptr = t.data_ptr()
-            for k, o in enumerate(P.outputs):
-                prm.out[k].ptr = outs[o.name].data_ptr()
+            sms = _sm_count()
             if P.kind == "flat":
                 U = flat_unroll(P)
                 items = math.prod(P.ext) // P.W
-                grid = max(1, min((items + 256 * U - 1) // (256 * U), sms * kernel.ctas_per_sm(256)))
-                kernel.launch(kernel.main, prm, grid, 256, stream)
+                geo = (max(1, min((items + 256 * U - 1) // (256 * U), sms * kernel.ctas_per_sm(256))), 256, 0, 0)
             else:
                 T, C, RPC, block = row_geometry(P)
                 ncol = sum(1 for o in P.outputs if o.kind == "col")
                 groups = (P.n_rows + RPC - 1) // RPC
                 grid = max(1, min(groups, sms * kernel.ctas_per_sm(block)))
-                scratch = None
-                if ncol:
-                    prm.nparts = grid * RPC
-                    scratch = torch.empty(ncol * grid * RPC * P.row_len, dtype=torch.float32, device=dev)
-                    prm.scratch = scratch.data_ptr()
-                kernel.launch(kernel.main, prm, grid, block, stream)
-                if ncol:
-                    kernel.launch(kernel.fold, prm, (P.row_len + 31) // 32, 256, stream)
+                geo = (grid, block, grid * RPC if ncol else 0, ncol * grid * RPC * P.row_len)
+            plan = (kernel, prm, threading.Lock(), geo)
+            if len(self._plans) < self.MAX_PLANS:
+                self._plans[key] = plan
+        kernel, prm, lock, (grid, block, nparts, scratch_elems) = plan
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        scratch = torch.empty(scratch_elems, dtype=torch.float32, device=dev) if scratch_elems else None
+        with lock, _on(dev):
+            for k, t in enumerate(tensors):
+                prm.inp[k].ptr = t.data_ptr()
+            for k, o in enumerate(P.outputs):
+                prm.out[k].ptr = outs[o.name].data_ptr()
+            if scratch is not None:
+                prm.nparts = nparts
+                prm.scratch = scratch.data_ptr()
+            kernel.launch(kernel.main, prm, grid, block, stream)
+            if scratch is not None:
+                kernel.launch(kernel.fold, prm, (P.row_len + 31) // 32, 256, stream)
         return result

@@ -29,25 +29,6 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
-// 2^x for x <= 0 on the FMA pipe (no MUFU): round-to-nearest split x = n + f with the 1.5 * 2^23 trick, a degree-6
-// polynomial for 2^f on [-0.5, 0.5] (relative error < 2e-8, below ex2.approx's own 2 ulp), n added into the exponent.
-// The forward is bound by the special-function unit (one ex2 per logit, 16 lanes per clock per SM against 128 FMA
-// lanes): kCePoly of every 8 logits take this path instead, which balances the two pipes.
-__device__ __forceinline__ float poly_exp2(float x) {
-    x = fmaxf(x, -125.f);
-    const float t = x + 12582912.f;
-    const float f = x - (t - 12582912.f);
-    float p = 1.5403530e-4f;
-    p = fmaf(p, f, 1.3333558e-3f);
-    p = fmaf(p, f, 9.6181291e-3f);
-    p = fmaf(p, f, 5.5504109e-2f);
-    p = fmaf(p, f, 2.4022651e-1f);
-    p = fmaf(p, f, 6.9314718e-1f);
-    p = fmaf(p, f, 1.0f);
-    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
-constexpr int kCePoly = 2;
-
 struct MS {
     float m, s;
 };
@@ -96,10 +77,7 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
                         // |x| * 2^-24 in the exponent, which is visible for large logits.
                         float s = acc.s * fast_exp2((acc.m - m) * kLog2e);
 #pragma unroll
-                        for (int e = 0; e < kE; ++e) {
-                            const float a = (f[e] - m) * kLog2e;
-                            s += (kE == 8 && e >= kE - kCePoly) ? poly_exp2(a) : fast_exp2(a);
-                        }
+                        for (int e = 0; e < kE; ++e) s += fast_exp2((f[e] - m) * kLog2e);
                         acc = {m, s};
                     }
                 }
