@@ -32,6 +32,14 @@ def region_census(thunder, jm):
     return out
 
 
+def _copy_stats(total_steps: int):
+    """Strided operands that a family launcher had to make dense first (b200ex.ops.COPY_STATS), per step."""
+    from b200ex import ops
+
+    c = ops.COPY_STATS
+    return {"copies_per_step": c["copies"] / max(total_steps, 1), "bytes_per_step": c["bytes"] / max(total_steps, 1)}
+
+
 def run(args, thunder, ClockSampler, dist=None, emit=True):
     """Runs the step benchmark.  With emit=True rank 0 prints the JSON line; otherwise the dict is returned (rank 0)
     or None (other ranks), and an already initialised process group `dist` is reused and left open."""
@@ -158,6 +166,7 @@ def run(args, thunder, ClockSampler, dist=None, emit=True):
             "model_tflops_per_gpu": flops / (step_ms / 1e3) / 1e12,
             "compile_s": compile_s, "peak_mem_gib": peak_mem, "final_loss": loss,
             "b200_launches_per_step": region_census(thunder, jm) if args.executor == "b200" else {},
+            "operand_copies": _copy_stats(args.steps + max(args.warmup, 3)) if args.executor == "b200" else None,
             "clocks": clocks,
         }
         if args.executor == "b200":

@@ -736,6 +736,8 @@ def main():
     ap.add_argument("--no-train-step", action="store_true", help="skip the Llama-3-8B-shape training step that the default run appends as `train_step`")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="time the step loop through the Python launchers instead of per-step CUDA graphs")
+    ap.add_argument("--profile", action="store_true", help="for ncu: W warm-up steps, then K plain steps (one launch per kernel per step), nothing else; "
+                                                            "numbers printed by such a run are not bench values")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.workload == "llama_step":
@@ -791,6 +793,15 @@ def main():
     # ---- whole-step throughput, inputs resident in HBM ------------------------------------------
     for i in range(args.warmup):
         wl.step(i)
+    if args.profile:
+        torch.cuda.synchronize(device)
+        for i in range(args.steps):
+            wl.step(i)
+        torch.cuda.synchronize(device)
+        if rank == 0:
+            sampler.stop()
+            _emit({"profile_run": True, "workload": wl.describe(), "steps": args.steps, "warmup": args.warmup, "launches_per_step": wl.launches_per_step})
+        return
     # One CUDA graph per buffer set, each holding one whole step (forward + backward launches): the timed loop
     # replays them round-robin, so a step costs one graph launch on the host instead of three Python launchers —
     # what the reference offers through CUDAGraphTransform.  --no-graph (or a failed capture) times the Python loop.

@@ -1290,21 +1290,19 @@ class B200Region:
         ins = set(self.input_names)
         steps, peeled_outs = [], set()
         for out in sorted(region_outs):
-            chain, name = [], out
+            # Walk inwards from the output for as long as the chain stays viewable: (outer) transposes / slices /
+            # expands, then reshapes of something dense.  The first prim that would put a reshape on top of a strided
+            # view ends the walk: its OUTPUT is the source, which a kernel of the region writes densely.
+            chain, name, seen_r = [], out, False
             while name in prod and prod[name].sym.id in self._VIEW_PRIMS and isinstance(prod[name].args[0], TensorProxy):
-                chain.append(prod[name])
-                name = self._resolve(prod[name].args[0].name)
-            if not chain or (name not in ins and name not in prod):
-                continue
-            # inner to outer: R* V*
-            seen_v, ok = False, True
-            for b in reversed(chain):
+                b = prod[name]
                 is_r = b.sym.id in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE)
-                if is_r and seen_v and b.sym.id == PrimIDs.RESHAPE:
-                    ok = False
+                if seen_r and not is_r:
                     break
-                seen_v = seen_v or not is_r
-            if not ok:
+                seen_r = seen_r or b.sym.id == PrimIDs.RESHAPE
+                chain.append(b)
+                name = self._resolve(b.args[0].name)
+            if not chain or (name not in ins and name not in prod):
                 continue
             fns = []
             for b in reversed(chain):

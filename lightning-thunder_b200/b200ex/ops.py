@@ -68,13 +68,24 @@ def _stream(dev: torch.device) -> int:
     return torch.cuda.current_stream(dev).cuda_stream
 
 
+# The family kernels take dense row-major operands.  A strided operand is copied first — a full extra read + write
+# that no roofline line of the kernel counts — so every such copy is counted here and reported by the benchmarks
+# (train_step's `operand_copies`); a correct model-level layout keeps both numbers at zero.  The generated region
+# kernels (b200ex/regionc.py) read strided operands in place instead.
+COPY_STATS = {"copies": 0, "bytes": 0}
+
+
 def _contig(t):
-    return t if t.is_contiguous() else t.contiguous()
+    if t.is_contiguous():
+        return t
+    COPY_STATS["copies"] += 1
+    COPY_STATS["bytes"] += 2 * t.numel() * t.element_size()
+    return t.contiguous()
 
 
 def _rows2d(t: torch.Tensor) -> torch.Tensor:
     """View as [rows, hidden]; makes a contiguous copy only if the layout is not already row-major."""
-    t = t if t.is_contiguous() else t.contiguous()
+    t = _contig(t)
     return t.view(-1, t.shape[-1]) if t.dim() > 0 else t.view(1, 1)
 
 
@@ -85,7 +96,7 @@ def rmsnorm_fwd(x, residual, weight, eps: float):
     shape = x.shape
     x2 = _rows2d(x)
     r2 = _rows2d(residual) if residual is not None else None
-    w = weight.contiguous() if weight is not None else None
+    w = _contig(weight) if weight is not None else None
     rows, hidden = x2.shape
     y = torch.empty_like(x2)
     h = torch.empty_like(x2) if residual is not None else None
@@ -105,8 +116,8 @@ def rmsnorm_bwd(dy, h, weight, rstd, dh_in=None):
     shape = h.shape
     dy2, h2 = _rows2d(dy), _rows2d(h)
     d2 = _rows2d(dh_in) if dh_in is not None else None
-    w = weight.contiguous() if weight is not None else None
-    rs = rstd.contiguous().view(-1)
+    w = _contig(weight) if weight is not None else None
+    rs = _contig(rstd).view(-1)
     rows, hidden = h2.shape
     dx = torch.empty_like(h2)
     dw = torch.empty_like(w) if w is not None else None

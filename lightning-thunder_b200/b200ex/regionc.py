@@ -1260,6 +1260,15 @@ def row_geometry(P: Program):
     sid = _leaf_sids(P)
     resident = sum(1 for k in range(len(P.leaves)) if P.full[sid[k]]) + sum(1 for o in P.outputs if o.kind == "col")
     cmax = 4 if resident <= 2 else (2 if resident <= 5 else 1)
+    if resident > 5:
+        # many operands, but 16-bit ones stay packed (4 registers per 8 elements): two chunks per thread still fit
+        # next to the second (prefetch) buffer, and a 256-thread CTA leaves room for two CTAs per SM
+        no = P.n_outer
+        per_row = [k for k in range(len(P.leaves)) if P.full[sid[k]] and any(v < no for c in P.leaves[k].coords for v, _ in c[0])]
+        cost = sum(4 if (P.leaves[k].dtype in (torch.bfloat16, torch.float16) and W == 8) else W for k in per_row)
+        fixed = (resident - len(per_row)) * W
+        if 2 * (2 * cost + fixed) <= 112:
+            cmax = 2
     T = 32
     while T < 1024 and (items + T - 1) // T > cmax:
         T *= 2
