@@ -1277,6 +1277,10 @@ class B200Region:
     # ---- outputs that are views ------------------------------------------------------------------------------------
     _VIEW_PRIMS = (PrimIDs.RESHAPE, PrimIDs.TRANSPOSE, PrimIDs.SLICE, PrimIDs.SQUEEZE, PrimIDs.BROADCAST_IN_DIM)
 
+    def _chain_has_stride_view(self, name: str, prod: dict) -> bool:
+        b = prod.get(name)
+        return b is not None and b.sym.id in self._VIEW_PRIMS and b.sym.id not in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE)
+
     def _peel_output_views(self, live: list[BoundSymbol], region_outs: set):
         """Region outputs that are views of a materialised value are not computed: they are returned as torch views
         of it, as the reference's torch executor returns them (torchex.py:562-630) — e.g. the [B*T, H] and [H, B*T]
@@ -1289,7 +1293,11 @@ class B200Region:
         prod = {o.name: b for b in live for o in _outs_of(b)}
         ins = set(self.input_names)
         steps, peeled_outs = [], set()
-        for out in sorted(region_outs):
+        # Chains with a transpose / slice / expand first (they always pay: the kernel writes the dense source instead of
+        # a strided copy); pure reshape chains only when their source is written anyway (an input, or already an
+        # output) — otherwise the reshape is free inside the kernel and peeling would only split its outputs by shape.
+        order = sorted(region_outs, key=lambda o: (0 if self._chain_has_stride_view(o, prod) else 1, o))
+        for out in order:
             # Walk inwards from the output for as long as the chain stays viewable: (outer) transposes / slices /
             # expands, then reshapes of something dense.  The first prim that would put a reshape on top of a strided
             # view ends the walk: its OUTPUT is the source, which a kernel of the region writes densely.
@@ -1303,6 +1311,8 @@ class B200Region:
                 chain.append(b)
                 name = self._resolve(b.args[0].name)
             if not chain or (name not in ins and name not in prod):
+                continue
+            if all(b.sym.id in (PrimIDs.RESHAPE, PrimIDs.SQUEEZE) for b in chain) and name not in ins and name not in region_outs:
                 continue
             fns = []
             for b in reversed(chain):

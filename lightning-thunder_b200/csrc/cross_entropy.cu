@@ -7,9 +7,14 @@
 // and the valid-target count.
 // Backward: one pass, reads logits, writes dlogits; log p is recomputed from the saved max and
 // log-sum and rounded to the storage dtype exactly where the reference holds it as a tensor.
+#include <cooperative_groups.h>
+
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace b200k {
 namespace {
@@ -40,7 +45,12 @@ __device__ __forceinline__ MS ms_merge(MS a, MS b) {
     return {m, sa + sb};
 }
 
-template <typename T>
+// kCluster CTAs share one row (thread-block cluster, launched with cudaLaunchAttributeClusterDimension): each streams
+// a 1/kCluster slice of the vocabulary, the non-leading CTAs deposit their (max, sum) pair in the leading CTA's shared
+// memory through distributed shared memory, and one cluster barrier later the leading CTA merges and writes the row's
+// results.  Used when there are too few rows to occupy the GPU with one CTA per row (a 128k-vocabulary row is 256 KB:
+// with a few hundred rows the single-CTA form leaves SMs idle or a ragged last wave); kCluster = 1 is the plain form.
+template <typename T, int kCluster>
 __global__ void __launch_bounds__(kCeThreads)
 ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, float* __restrict__ row_max,
               float* __restrict__ row_logsum, float* __restrict__ row_nll, int64_t rows, int64_t vocab, int64_t ignore_index,
@@ -48,24 +58,31 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
     using V = Vec<T>;
     constexpr int kE = V::kElems;
     __shared__ float sm_m[kCeThreads / 32], sm_s[kCeThreads / 32];
+    __shared__ float peer_m[8], peer_s[8];  // slot r: the pair of cluster rank r (written remotely)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t nvec = vec_ok ? vocab / kE : 0;
+    const int crank = kCluster > 1 ? static_cast<int>(cg::this_cluster().block_rank()) : 0;
+    const int64_t first_row = kCluster > 1 ? blockIdx.x / kCluster : blockIdx.x;
+    const int64_t row_step = kCluster > 1 ? gridDim.x / kCluster : gridDim.x;
+    // this CTA's slice of the row's vectors
+    const int64_t v0 = kCluster > 1 ? nvec * crank / kCluster : 0;
+    const int64_t v1 = kCluster > 1 ? nvec * (crank + 1) / kCluster : nvec;
 
-    for (int64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    for (int64_t row = first_row; row < rows; row += row_step) {
         const T* x = logits + row * vocab;
         MS acc = {-INFINITY, 0.f};
         // vectorised body
-        for (int64_t base = tid; base < nvec; base += kCeThreads * kCeUnroll) {
+        for (int64_t base = v0 + tid; base < v1; base += kCeThreads * kCeUnroll) {
             uint4 v[kCeUnroll];
 #pragma unroll
             for (int u = 0; u < kCeUnroll; ++u) {
                 const int64_t i = base + static_cast<int64_t>(u) * kCeThreads;
-                if (i < nvec) v[u] = ld_stream(reinterpret_cast<const uint4*>(x) + i);
+                if (i < v1) v[u] = ld_stream(reinterpret_cast<const uint4*>(x) + i);
             }
 #pragma unroll
             for (int u = 0; u < kCeUnroll; ++u) {
                 const int64_t i = base + static_cast<int64_t>(u) * kCeThreads;
-                if (i < nvec) {
+                if (i < v1) {
                     float f[kE];
                     V::unpack(v[u], f);
                     float mx = f[0];
@@ -83,10 +100,12 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
                 }
             }
         }
-        // scalar tail (vocab not a multiple of the vector width, or unaligned rows)
-        for (int64_t j = nvec * kE + tid; j < vocab; j += kCeThreads) {
-            const float f = V::load1(x, j);
-            acc = ms_merge(acc, MS{f, 1.f});
+        // scalar tail (vocab not a multiple of the vector width, or unaligned rows): the leading CTA's
+        if (crank == 0) {
+            for (int64_t j = nvec * kE + tid; j < vocab; j += kCeThreads) {
+                const float f = V::load1(x, j);
+                acc = ms_merge(acc, MS{f, 1.f});
+            }
         }
         // CTA merge
 #pragma unroll
@@ -99,32 +118,46 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
             sm_s[warp] = acc.s;
         }
         __syncthreads();
+        MS t = {-INFINITY, 0.f};
         if (warp == 0) {
-            MS t = lane < kCeThreads / 32 ? MS{sm_m[lane], sm_s[lane]} : MS{-INFINITY, 0.f};
+            t = lane < kCeThreads / 32 ? MS{sm_m[lane], sm_s[lane]} : MS{-INFINITY, 0.f};
 #pragma unroll
             for (int o = 8; o > 0; o >>= 1) {
                 MS other = {__shfl_xor_sync(0xffffffffu, t.m, o), __shfl_xor_sync(0xffffffffu, t.s, o)};
                 t = ms_merge(t, other);
             }
-            if (lane == 0) {
-                const float logsum = logf(t.s);
-                row_max[row] = t.m;
-                row_logsum[row] = logsum;
-                const int64_t tg = target[row];
-                float nll = 0.f;
-                if (tg != ignore_index && (tg < 0 || tg >= vocab)) {
-                    // ATen's nll_loss device-asserts on a class index outside [0, vocab) (the reference's oracle path,
-                    // torchex.py:1731-1783); same contract here: report and trap, never score the row as 0.
-                    printf("b200k_cross_entropy_fwd: target %lld of row %lld is outside [0, %lld)\n", (long long)tg, (long long)row, (long long)vocab);
-                    __trap();
-                }
-                if (tg != ignore_index) {
-                    // -log p of the target, rounded through the storage dtype like the reference's log_softmax output
-                    nll = -V::rnd((V::load1(x, tg) - t.m) - logsum);
-                }
-                row_nll[row] = nll;
+            if (kCluster > 1 && lane == 0 && crank != 0) {
+                // hand this CTA's pair to the leading CTA of the cluster (distributed shared memory)
+                cg::cluster_group cl = cg::this_cluster();
+                *cl.map_shared_rank(&peer_m[crank], 0) = t.m;
+                *cl.map_shared_rank(&peer_s[crank], 0) = t.s;
             }
         }
+        // every thread of every CTA of the cluster takes part in the cluster barrier; after it the remote stores are
+        // visible to the leading CTA
+        if (kCluster > 1) cg::this_cluster().sync();
+        if (warp == 0 && lane == 0 && crank == 0) {
+#pragma unroll
+            for (int r = 1; r < kCluster; ++r) t = ms_merge(t, MS{peer_m[r], peer_s[r]});
+            const float logsum = logf(t.s);
+            row_max[row] = t.m;
+            row_logsum[row] = logsum;
+            const int64_t tg = target[row];
+            float nll = 0.f;
+            if (tg != ignore_index && (tg < 0 || tg >= vocab)) {
+                // ATen's nll_loss device-asserts on a class index outside [0, vocab) (the reference's oracle path,
+                // torchex.py:1731-1783); same contract here: report and trap, never score the row as 0.
+                printf("b200k_cross_entropy_fwd: target %lld of row %lld is outside [0, %lld)\n", (long long)tg, (long long)row, (long long)vocab);
+                __trap();
+            }
+            if (tg != ignore_index) {
+                // -log p of the target, rounded through the storage dtype like the reference's log_softmax output
+                nll = -V::rnd((V::load1(x, tg) - t.m) - logsum);
+            }
+            row_nll[row] = nll;
+        }
+        // the peers' slots are free for the next row only after the leading CTA has read them
+        if (kCluster > 1) cg::this_cluster().sync();
         __syncthreads();
     }
 }
@@ -249,9 +282,35 @@ int run_fwd(const void* logits, const int64_t* target, float* row_max, float* ro
     const int vec_ok = aligned16(logits) && vocab % kE == 0;
     if (rows > 0) {
         const int64_t cap = static_cast<int64_t>(sm_count()) * 4;
-        const int grid = static_cast<int>(rows < cap ? rows : cap);
-        ce_fwd_kernel<T><<<grid, kCeThreads, 0, st>>>(static_cast<const T*>(logits), target, row_max, row_logsum, row_nll, rows, vocab,
-                                                      ignore_index, vec_ok);
+        // Few long rows: a 2- or 4-CTA cluster per row (DSMEM merge) instead of idle SMs.  B200K_CE_CLUSTER=1|2|4 pins it.
+        int cluster = 1;
+        if (vec_ok && vocab >= 32768) cluster = rows * 4 <= cap ? 4 : (rows * 2 <= cap ? 2 : 1);
+        if (const char* e = getenv("B200K_CE_CLUSTER")) {
+            const int v = atoi(e);
+            if (vec_ok && (v == 1 || v == 2 || v == 4)) cluster = v;
+        }
+        if (cluster == 1) {
+            const int grid = static_cast<int>(rows < cap ? rows : cap);
+            ce_fwd_kernel<T, 1><<<grid, kCeThreads, 0, st>>>(static_cast<const T*>(logits), target, row_max, row_logsum, row_nll, rows,
+                                                             vocab, ignore_index, vec_ok);
+        } else {
+            const int64_t want = rows * cluster, lim = cap / cluster * cluster;
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(static_cast<unsigned>(want < lim ? want : lim));
+            cfg.blockDim = dim3(kCeThreads);
+            cfg.stream = st;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = static_cast<unsigned>(cluster);
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            const T* lg = static_cast<const T*>(logits);
+            cudaError_t e = cluster == 2 ? cudaLaunchKernelEx(&cfg, ce_fwd_kernel<T, 2>, lg, target, row_max, row_logsum, row_nll, rows, vocab, ignore_index, vec_ok)
+                                         : cudaLaunchKernelEx(&cfg, ce_fwd_kernel<T, 4>, lg, target, row_max, row_logsum, row_nll, rows, vocab, ignore_index, vec_ok);
+            if (e != cudaSuccess) return static_cast<int>(e);
+        }
         if (int rc = launch_status()) return rc;
     }
     if (loss != nullptr) {

@@ -177,3 +177,33 @@ def test_out_of_range_target_traps_like_aten():
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert "CUDA ERROR" in r.stdout and "NO ERROR" not in r.stdout, (r.stdout, r.stderr[-500:])
     assert "outside [0, 64)" in r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("cluster", [2, 4])
+@pytest.mark.parametrize("rows,vocab", [(3, 128256), (64, 40000), (300, 128256)])
+def test_forward_on_thread_block_clusters(cluster, rows, vocab):
+    """Few long rows: 2 or 4 CTAs of a thread-block cluster share a row and merge their (max, sum) pairs through
+    distributed shared memory.  Same results as the oracle (and as the one-CTA form) within the usual bounds."""
+    import os
+
+    g = torch.Generator().manual_seed(rows + vocab)
+    logits = (torch.randn(rows, vocab, generator=g) * 3).to(torch.bfloat16)
+    target = torch.randint(0, vocab, (rows,), generator=g)
+    target[1] = -100
+    os.environ["B200K_CE_CLUSTER"] = str(cluster)
+    try:
+        _check(logits, target, torch.tensor(1.0, dtype=torch.bfloat16), -100, f"cluster {cluster} {rows}x{vocab}")
+        got = _cuda(logits, target, torch.tensor(1.0, dtype=torch.bfloat16), -100)
+        os.environ["B200K_CE_CLUSTER"] = "1"
+        one = _cuda(logits, target, torch.tensor(1.0, dtype=torch.bfloat16), -100)
+    finally:
+        os.environ.pop("B200K_CE_CLUSTER", None)
+    assert torch.equal(got[1].cpu(), one[1].cpu())  # row max: exact either way
+    torch.testing.assert_close(got[2].cpu(), one[2].cpu(), rtol=1e-6, atol=1e-6)  # log-sum: another merge order
+
+
+def test_default_policy_uses_clusters_for_few_rows():
+    g = torch.Generator().manual_seed(1)
+    logits = (torch.randn(100, 128256, generator=g) * 2).to(torch.bfloat16)
+    target = torch.randint(0, 128256, (100,), generator=g)
+    _check(logits, target, torch.tensor(1.0, dtype=torch.bfloat16), -100, "100x128256 (4-CTA clusters by default)")

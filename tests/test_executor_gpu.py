@@ -336,11 +336,16 @@ def test_readme_mlp_fp32_on_the_gpu():
         torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6)
 
 
-def _grads_close(results, tol=1.6e-2):
+def _grads_close(results, tol=1.6e-2, zero_in_exact_arithmetic=()):
     """Parameter gradients: elementwise at rtol 1.6e-2 plus one bf16 ulp of the gradient tensor's largest magnitude (one
     differently rounded term of the sums they are), and norm-wise within rtol."""
     for n, g in results["b200"][1].items():
         ref = results["torch"][1][n]
+        if n in zero_in_exact_arithmetic:
+            # both runs hold nothing but rounding noise here (e.g. a key-projection bias under softmax): same size of
+            # noise, no element-wise claim
+            assert g.float().abs().max().item() <= 4.0 * ref.float().abs().max().item() + 1e-12, f"grad {n}"
+            continue
         # norm-wise, with one bf16 ulp of the tensor's scale on every element as the floor (a gradient that is zero
         # in exact arithmetic — a key-projection bias under softmax — is rounding noise in both runs)
         floor = 2.0**-8 * ref.float().abs().max() * ref.numel() ** 0.5
@@ -402,4 +407,4 @@ def test_reference_bart_self_attention():
     assert "b200_softmax_fwd" in fk
     err = (results["b200"][0].float() - results["torch"][0].float()).norm() / results["torch"][0].float().norm()
     assert err.item() < 1e-2
-    _grads_close(results)
+    _grads_close(results, zero_in_exact_arithmetic=("k_proj.bias",))

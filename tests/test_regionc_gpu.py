@@ -215,7 +215,9 @@ def test_llama3_8b_block_in_litgpt_spelling_full_size():
     x0 = (torch.randn(B, T, cfg.n_embd, device=DEV) * 0.5).to(BF)
     cot = torch.randn(B, T, cfg.n_embd, device=DEV).to(BF)
     res = {}
-    for name, execs in (("b200", [sdpa_ex, b200.ex]), ("torch", [sdpa_ex, "torch"])):
+    from baseline.attention import cudnn_sdpa_ex  # the attention executor list of the training benchmark (both arms)
+
+    for name, execs in (("b200", [cudnn_sdpa_ex, sdpa_ex, b200.ex]), ("torch", [cudnn_sdpa_ex, sdpa_ex, "torch"])):
         block.zero_grad(set_to_none=True)
         x = x0.clone().requires_grad_(True)
         jb = thunder.jit(block, executors=execs)
