@@ -330,7 +330,7 @@ class B200Executor(FusionExecutor):
             if len(n.group_bsyms) > 1:
                 return True
             b = n.group_bsyms[0]
-            return self.can_fuse(b) and self._has_cuda_tensor(b)
+            return self.can_fuse(b) and self._has_cuda_tensor(b) and b.sym.id not in _NEVER_FUSE
 
         # Partitioning: the reference's `fusion_type` option wins when the user sets it; otherwise b200 defaults to the
         # dataflow partitioner (data_dependent_partition.py:339-343), which keeps chains that a matmul interleaves
@@ -353,7 +353,7 @@ class B200Executor(FusionExecutor):
                 continue
             if len(bsyms) == 1:
                 b = bsyms[0]
-                if not (self.can_fuse(b) and self._has_cuda_tensor(b)):
+                if not (self.can_fuse(b) and self._has_cuda_tensor(b)) or b.sym.id in _NEVER_FUSE:
                     fused.append(b)
                     continue
             if len(bsyms) < min_region or not self.can_lower(bsyms):
@@ -988,17 +988,53 @@ def _synchronize_grad(a, group, distparallel_type):
     if get_skip_data_parallel_grad_sync() and distparallel_type == DistParallelType.REPLICATED:
         put_grads((a,), (g,))
         return out
-    ops_ = dist_prims.DistributedReduceOps
     if _sync_uses_avg(group):
-        op, src = ops_.AVG, g
+        # the reference's torch executor only maps SUM and MAX (thunder/torch/__init__.py:6421-6424), so the averaging
+        # collectives are executor operators of ours; they return the same (work, tensor) future as the reference's
+        # impls, and the reference's own `wait` prim completes them
+        if distparallel_type == DistParallelType.FULLY_SHARDED:
+            synced = b200_reduce_scatter_avg(g, group).wait()
+        else:
+            synced = b200_all_reduce_avg(g, group).wait()
     else:
-        op, src = ops_.SUM, g / group.size()
-    if distparallel_type == DistParallelType.FULLY_SHARDED:
-        synced = dist_prims.reduce_scatter(src, op, group, do_async=True).wait()
-    else:
-        synced = dist_prims.all_reduce(src, op, group, do_async=True).wait()
+        src = g / group.size()
+        if distparallel_type == DistParallelType.FULLY_SHARDED:
+            synced = dist_prims.reduce_scatter(src, dist_prims.DistributedReduceOps.SUM, group, do_async=True).wait()
+        else:
+            synced = dist_prims.all_reduce(src, dist_prims.DistributedReduceOps.SUM, group, do_async=True).wait()
     put_grads((a,), (synced,))
     return out
+
+
+def _rs_avg_meta(a, group):
+    from thunder.core.proxies import FutureTensorProxy
+
+    utils.check(a.shape[0] % group.size() == 0, lambda: f"b200_reduce_scatter_avg: dim 0 of {tuple(a.shape)} is not divisible by the group size {group.size()}")
+    return FutureTensorProxy(like=a, shape=(a.shape[0] // group.size(),) + tuple(a.shape[1:]))
+
+
+def _rs_avg_impl(a, group):
+    out = torch.empty((a.shape[0] // group.size(),) + tuple(a.shape[1:]), dtype=a.dtype, device=a.device)
+    handle = torch.distributed.reduce_scatter_tensor(out, a.contiguous(), torch.distributed.ReduceOp.AVG, group, async_op=True)
+    return handle, out
+
+
+def _ar_avg_meta(a, group):
+    from thunder.core.proxies import FutureTensorProxy
+
+    return FutureTensorProxy(like=a)
+
+
+def _ar_avg_impl(a, group):
+    c = a.clone()  # like the reference's impl (torchex.py:2063-2080): the trace is functional, `a` may be read again
+    handle = torch.distributed.all_reduce(c, torch.distributed.ReduceOp.AVG, group, async_op=True)
+    return handle, c
+
+
+b200_reduce_scatter_avg = ex.register_operator("b200_reduce_scatter_avg", meta=_rs_avg_meta, fn=_rs_avg_impl)
+b200_all_reduce_avg = ex.register_operator("b200_all_reduce_avg", meta=_ar_avg_meta, fn=_ar_avg_impl)
+# launched where they stand in the trace, never inside a fusion region (their output is a future, not a tensor)
+_NEVER_FUSE = {b200_reduce_scatter_avg.id, b200_all_reduce_avg.id}
 
 
 def _register_synchronize() -> None:
