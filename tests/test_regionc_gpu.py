@@ -240,3 +240,28 @@ def test_llama3_8b_block_in_litgpt_spelling_full_size():
     for n, g in res["b200"][2].items():
         assert rel(g, res["torch"][2][n]) < 1.6e-2, f"grad {n}"
         assert_tensor_scale_parity(g, res["torch"][2][n], what=f"grad {n}")
+
+
+def test_unvectorisable_pointwise_launches_use_the_gather_kernel_not_the_interpreter():
+    """Inner extents that are not a multiple of 8, transposed operands, misaligned views: the elementwise path hands
+    such launches to a generated gather kernel (narrower or element-wise loads) instead of the ahead-of-time
+    interpreter, which decodes its program per element."""
+    from b200ex.pointwise import PwLaunch
+
+    g = torch.Generator(device=DEV).manual_seed(3)
+    x = torch.randn(37, 33, generator=g, device=DEV).to(BF)
+    yt = torch.randn(33, 37, generator=g, device=DEV).to(BF).t()   # inner stride 37
+    base = torch.randn(37 * 33 + 3, generator=g, device=DEV).to(BF)
+    z = base[3:].view(37, 33)                                        # 6-byte aligned start
+    fn = lambda x, y, z: torch.tanh(x) * y + z * 0.5
+    jf = thunder.jit(fn, executors=[b200.ex])
+    got = jf(x, yt, z)
+    want = thunder.jit(fn, executors=["torch"])(x, yt, z)
+    assert torch.equal(got, want)
+    launches = []
+    for bs in thunder.last_traces(jf)[-1].bound_symbols:
+        if bs.sym.is_fusion and bs.sym.name.startswith("b200Fusion"):
+            for st in bs._call_ctx[bs.sym.name].steps:
+                d = getattr(st.run, "__defaults__", None) or ()
+                launches += [o for o in d if isinstance(o, PwLaunch)]
+    assert launches and all(l.gather_launches >= 1 and l.jit_launches == 0 for l in launches)
