@@ -795,9 +795,11 @@ def main():
         wl.step(i)
     if args.profile:
         torch.cuda.synchronize(device)
+        torch.cuda.profiler.start()  # ncu --profile-from-start off captures exactly these K steps
         for i in range(args.steps):
             wl.step(i)
         torch.cuda.synchronize(device)
+        torch.cuda.profiler.stop()
         if rank == 0:
             sampler.stop()
             _emit({"profile_run": True, "workload": wl.describe(), "steps": args.steps, "warmup": args.warmup, "launches_per_step": wl.launches_per_step})

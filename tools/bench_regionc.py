@@ -96,6 +96,36 @@ def main():
     for name, region, ins, outs in region_callables(jf):
         us, nb = time_region(region, ins, outs)
         rows.append(("litgpt RMSNorm + residual (plain torch ops) " + name, region.launch_kinds, us, nb))
+    # LayerNorm spelled with torch ops (mean / var / rsqrt), [8192 x 4096] bf16
+    xl = torch.randn(R, H, generator=g, device=DEV).to(torch.bfloat16).requires_grad_(True)
+    wl, bl = (torch.randn(H, generator=g, device=DEV).to(torch.bfloat16).requires_grad_(True) for _ in range(2))
+
+    def ln(x, w, b):
+        xf = x.float()
+        mu = xf.mean(-1, keepdim=True)
+        var = ((xf - mu) ** 2).mean(-1, keepdim=True)
+        return ((xf - mu) * torch.rsqrt(var + 1e-5) * w.float() + b.float()).to(x.dtype)
+
+    jf = thunder.jit(ln, executors=[b200.ex])
+    yl = jf(xl, wl, bl)
+    torch.autograd.grad([yl], [xl, wl, bl], [torch.ones_like(yl)])
+    for name, region, ins, outs in region_callables(jf):
+        us, nb = time_region(region, ins, outs)
+        rows.append(("LayerNorm (plain torch ops) " + name, region.launch_kinds, us, nb))
+    # softmax over the last dim spelled with exp / sum, [16384 x 2048] bf16 (amax's backward stays partly with torch)
+    xs = torch.randn(16384, 2048, generator=g, device=DEV).to(torch.bfloat16).requires_grad_(True)
+
+    def sm(x):
+        xf = x.float()
+        e = torch.exp(xf - xf.amax(-1, keepdim=True))
+        return (e / e.sum(-1, keepdim=True)).to(x.dtype)
+
+    jf = thunder.jit(sm, executors=[b200.ex])
+    ys = jf(xs)
+    torch.autograd.grad([ys], [xs], [torch.ones_like(ys)])
+    for name, region, ins, outs in region_callables(jf):
+        us, nb = time_region(region, ins, outs)
+        rows.append(("softmax (plain torch ops) " + name, region.launch_kinds, us, nb))
     print(f"{'region':64s} {'launches':40s} {'us':>8s} {'MB':>8s} {'GB/s':>8s} {'frac':>6s}")
     for name, k, us, nb in rows:
         print(f"{name:64s} {','.join(k):40s} {us:8.1f} {nb / 1e6:8.1f} {nb / us / 1e3:8.0f} {nb / us / 1e3 / peak:6.2f}")
