@@ -942,7 +942,7 @@ def main():
         dom = max(kernels, key=lambda k: k["us_per_launch"])
         traffic = None
         try:
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
                 traffic = json.load(f).get(dom["kernel"])
         except Exception:
             pass
@@ -957,7 +957,7 @@ def main():
                        "sharding": "each rank runs the region on its own micro-batch; no data-path collective", "launch": launch_mode},
             "roofline": {"bound": "hbm", "kernel": dom["kernel"], "achieved": dom["achieved_gbps"], "peak": peak, "unit": UNIT,
                          "frac": dom["achieved_gbps"] / peak, "frac_of_nominal_8TBps": dom["achieved_gbps"] / 8000.0,
-                         "traffic": traffic, "traffic_source": "ncu --set full capture, profiles/r1_traffic.json" if traffic else None,
+                         "traffic": traffic, "traffic_source": "ncu --set full capture, profiles/r2_traffic.json" if traffic else None,
                          "algorithmic_bytes": dom["algorithmic_bytes"], "peak_source": peak_src},
             "kernels": kernels,
             "cpu_baseline": cpu,

@@ -79,42 +79,51 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
                 const int64_t i = base + static_cast<int64_t>(u) * kCeThreads;
                 if (i < v1) v[u] = ld_stream(reinterpret_cast<const uint4*>(x) + i);
             }
+            // One running-max update (and one rescale of the running sum) per batch of kCeUnroll vectors, not per
+            // vector: the kernel is bound by the special-function unit (ncu: XU pipe 72 %), and the rescale's ex2 is
+            // one MUFU in nine when it is paid per vector.
+            float mx = -INFINITY;
 #pragma unroll
             for (int u = 0; u < kCeUnroll; ++u) {
                 const int64_t i = base + static_cast<int64_t>(u) * kCeThreads;
                 if (i < v1) {
                     float f[kE];
                     V::unpack(v[u], f);
-                    float mx = f[0];
 #pragma unroll
-                    for (int e = 1; e < kE; ++e) mx = fmaxf(mx, f[e]);
-                    const float m = fmaxf(acc.m, mx);
-                    if (m != -INFINITY) {
-                        float s = acc.s * fast_exp2((acc.m - m) * kLog2e);
-                        if (kE == 8 && fabsf(m) <= 64.f) {
-                            // Packed form (two logits per FFMA2 / FADD2): x * log2e - m * log2e.  Scaling x and m
-                            // separately loses up to |m| * log2e * 2^-24 in the exponent — below 6e-6 here, i.e. under
-                            // 4e-6 relative on a term, far inside the fp32 tolerance of the log-sum.  The kernel is
-                            // issue-bound (ALU + MUFU), so halving the fp32 instruction count is what moves it.
-                            const float2 c2 = make_float2(kLog2e, kLog2e);
-                            const float nm = -(m * kLog2e);
-                            const float2 nm2 = make_float2(nm, nm);
-                            float2 s2 = make_float2(s, 0.f);
+                    for (int e = 0; e < kE; ++e) mx = fmaxf(mx, f[e]);
+                }
+            }
+            const float m = fmaxf(acc.m, mx);
+            if (m != -INFINITY) {
+                float s = acc.s * fast_exp2((acc.m - m) * kLog2e);
+                const bool packed = kE == 8 && fabsf(m) <= 64.f;
+                // Packed form (two logits per FFMA2 / FADD2): x * log2e - m * log2e.  Scaling x and m separately
+                // loses up to |m| * log2e * 2^-24 in the exponent — below 6e-6 for |m| <= 64, i.e. under 4e-6 relative
+                // on a term, far inside the fp32 tolerance of the log-sum.  Otherwise (x - m) first: exact for the
+                // terms that matter.
+                const float2 c2 = make_float2(kLog2e, kLog2e);
+                const float nm = -(m * kLog2e);
+                const float2 nm2 = make_float2(nm, nm);
+                float2 s2 = make_float2(s, 0.f);
 #pragma unroll
-                            for (int e = 0; e < kE; e += 2) {
+                for (int u = 0; u < kCeUnroll; ++u) {
+                    const int64_t i = base + static_cast<int64_t>(u) * kCeThreads;
+                    if (i < v1) {
+                        float f[kE];
+                        V::unpack(v[u], f);
+                        if (packed) {
+#pragma unroll
+                            for (int e = 0; e + 1 < kE; e += 2) {
                                 const float2 a = __ffma2_rn(make_float2(f[e], f[e + 1]), c2, nm2);
                                 s2 = __fadd2_rn(s2, make_float2(fast_exp2(a.x), fast_exp2(a.y)));
                             }
-                            s = s2.x + s2.y;
                         } else {
-                            // (x - m) first: exact for the terms that matter; for large logits the packed form's error
-                            // in the exponent would be visible.
 #pragma unroll
-                            for (int e = 0; e < kE; ++e) s += fast_exp2((f[e] - m) * kLog2e);
+                            for (int e = 0; e < kE; ++e) s2.x += fast_exp2((f[e] - m) * kLog2e);
                         }
-                        acc = {m, s};
                     }
                 }
+                acc = {m, s2.x + s2.y};
             }
         }
         // scalar tail (vocab not a multiple of the vector width, or unaligned rows): the leading CTA's

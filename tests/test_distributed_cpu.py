@@ -69,3 +69,54 @@ def test_ddp_gloo_world_size_2_with_b200_in_the_executor_list():
         ok, has_allreduce = open(result_file).read().split()
     assert ok == "1", "gradients after ddp differ from the mean of the per-rank gradients"
     assert has_allreduce == "1", "the data-parallel all_reduce is missing from the backward trace"
+
+
+def _fsdp_worker(rank, world, init_file, result_file):
+    import warnings
+
+    warnings.simplefilter("ignore")
+    thunder, b200 = import_thunder()
+    from thunder.distributed import fsdp
+
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", init_method=f"file://{init_file}", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        model = torch.nn.Sequential(torch.nn.Linear(16, 32, bias=False), torch.nn.GELU(), torch.nn.Linear(32, 4, bias=False))
+        ref = [p.detach().clone() for p in model.parameters()]
+        jm = fsdp(thunder.jit(model, executors=[b200.ex]), device=torch.device("cpu"))
+        g = torch.Generator().manual_seed(100 + rank)
+        x = torch.randn(8, 16, generator=g)
+        jm(x).square().mean().backward()
+        shards = [p.grad.detach().clone() for p in jm.parameters()]
+        local = torch.nn.Sequential(torch.nn.Linear(16, 32, bias=False), torch.nn.GELU(), torch.nn.Linear(32, 4, bias=False))
+        with torch.no_grad():
+            for p, r in zip(local.parameters(), ref):
+                p.copy_(r)
+        expect = []
+        for rk in range(world):
+            local.zero_grad()
+            xr = torch.randn(8, 16, generator=torch.Generator().manual_seed(100 + rk))
+            local(xr).square().mean().backward()
+            expect.append([p.grad.clone() for p in local.parameters()])
+        mean = [sum(gs) / world for gs in zip(*expect)]
+        # ZeRO: every rank holds the dim-0 shard of the averaged gradient
+        ok = all(torch.allclose(s, m.chunk(world, 0)[rank], rtol=1e-4, atol=1e-5) for s, m in zip(shards, mean))
+        bw = str(thunder.last_backward_traces(jm)[-1])
+        if rank == 0:
+            with open(result_file, "w") as f:
+                f.write(f"{int(ok)} {int('reduce_scatter' in bw)}")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_fsdp_gloo_world_size_2_gradient_shards_are_the_mean_over_ranks():
+    """thunder.distributed.fsdp with b200 in the executor list: b200's rule for dist_prims.synchronize (the reference's
+    spelling on a backend without AVG) all-gathers the parameter shards forward and reduce-scatters the gradients."""
+    with tempfile.TemporaryDirectory() as d:
+        init_file, result_file = os.path.join(d, "init"), os.path.join(d, "result")
+        mp.spawn(_fsdp_worker, args=(2, init_file, result_file), nprocs=2, join=True)
+        ok, has_rs = open(result_file).read().split()
+    assert ok == "1", "gradient shards after fsdp differ from the shard of the mean of the per-rank gradients"
+    assert has_rs == "1", "the reduce_scatter is missing from the backward trace"
