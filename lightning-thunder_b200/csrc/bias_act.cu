@@ -14,7 +14,7 @@
 namespace b200k {
 namespace {
 
-constexpr int kBaThreads = 512;
+constexpr int kBaThreads = 416;
 constexpr int kBaVpl = 2;
 constexpr int kBaRowParts = 4;  // CTAs per SM along rows (sizes the scratch)
 constexpr float kInvSqrt2 = 0.70710678118654752440f;
@@ -181,7 +181,7 @@ __device__ __forceinline__ uint32_t gelu_bwd_word(uint32_t a2, uint32_t g2) {
 // kAccum: keep fp32 column sums of the (rounded) backward result for dbias; kStore: write `out`;
 // pre_out (forward, nullable): also write the rounded pre-activation a = x + bias, which is what autodiff saves.
 template <typename T, int kAct, bool kHasBias, bool kBwd, bool kAccum, bool kStore = true, bool kPacked = false>
-__global__ void __launch_bounds__(kBaThreads)
+__global__ void __launch_bounds__(kBaThreads, 2)
 bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __restrict__ g, T* __restrict__ out,
                 T* __restrict__ pre_out, float* __restrict__ partial, int64_t rows, int nvec) {
     using V = Vec<T>;
