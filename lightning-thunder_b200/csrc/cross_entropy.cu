@@ -34,25 +34,6 @@ __device__ __forceinline__ float fast_exp2(float x) {
     return y;
 }
 
-// 2^x for x <= 0 on the FMA pipe (no MUFU): round-to-nearest split x = n + f with the 1.5 * 2^23 trick, a degree-6
-// polynomial for 2^f on [-0.5, 0.5] (relative error 2.4e-7, the size of ex2.approx's own 2 ulp), n added into the
-// exponent.  The forward is bound by the special-function unit (ncu: XU pipe 72 %, ALU 41 %): kCePoly of every 8
-// logits take this path and move a slice of the exponentials onto the pipe that has room.
-__device__ __forceinline__ float poly_exp2(float x) {
-    x = fmaxf(x, -125.f);
-    const float t = x + 12582912.f;
-    const float f = x - (t - 12582912.f);
-    float p = 1.5403530e-4f;
-    p = fmaf(p, f, 1.3333558e-3f);
-    p = fmaf(p, f, 9.6181291e-3f);
-    p = fmaf(p, f, 5.5504109e-2f);
-    p = fmaf(p, f, 2.4022651e-1f);
-    p = fmaf(p, f, 6.9314718e-1f);
-    p = fmaf(p, f, 1.0f);
-    return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
-constexpr int kCePoly = 1;
-
 struct MS {
     float m, s;
 };
@@ -100,7 +81,8 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
             }
             // One running-max update (and one rescale of the running sum) per batch of kCeUnroll vectors, not per
             // vector: the kernel is bound by the special-function unit (ncu: XU pipe 72 %), and the rescale's ex2 is
-            // one MUFU in nine when it is paid per vector.
+            // one MUFU in nine when it is paid per vector (391 -> 364 us).  Moving a share of the exponentials onto the
+            // FMA pipe (Cody-Waite split + degree-6 polynomial) was measured twice and is slower (401 / 413 us).
             float mx = -INFINITY;
 #pragma unroll
             for (int u = 0; u < kCeUnroll; ++u) {
@@ -134,8 +116,7 @@ ce_fwd_kernel(const T* __restrict__ logits, const int64_t* __restrict__ target, 
 #pragma unroll
                             for (int e = 0; e + 1 < kE; e += 2) {
                                 const float2 a = __ffma2_rn(make_float2(f[e], f[e + 1]), c2, nm2);
-                                const float ey = (kCePoly > 0 && e == kE - 2) ? poly_exp2(a.y) : fast_exp2(a.y);
-                                s2 = __fadd2_rn(s2, make_float2(fast_exp2(a.x), ey));
+                                s2 = __fadd2_rn(s2, make_float2(fast_exp2(a.x), fast_exp2(a.y)));
                             }
                         } else {
 #pragma unroll
