@@ -974,27 +974,41 @@ class _Gen:
         return str(dict(self.leaf_aff(k)[0]).get(self.vd, 0))
 
     def emit_elements(self, L, ind, W, ids, ref, leafref, predref, tail):
-        """The per-element loop: values `ids` for every element of the chunk, two elements per trip so that roundings
-        to a 16-bit format convert a pair at once (one cvt.rn.x2 instead of two).  ref(a, lane) names an operand,
+        """The per-element loop: values `ids` for every element of the chunk, two elements per trip.  A pair lives in
+        one float2: add / sub / mul are sm_100's packed fp32x2 instructions (`FADD2` / `FFMA2` / `FMUL2`, bit-identical
+        to the scalar round-to-nearest ops, half the issue slots), roundings to a 16-bit format convert the pair at
+        once (`cvt.rn.bf16x2`), everything else runs per lane.  ref(a, lane) names an operand (lane ".x" / ".y" / ""),
         leafref(k, e) reads element e of leaf k, tail(lane, e) -> extra lines per element (stores, partial sums)."""
-        lanes = [("_0", "e"), ("_1", "e + 1")] if W >= 2 else [("", "e")]
+        pair = W >= 2
+        lanes = [(".x", "e"), (".y", "e + 1")] if pair else [("", "e")]
         L.append(f"{ind}#pragma unroll")
         L.append(f"{ind}for (int e = 0; e < {W}; e += {len(lanes)}) {{")
+        both = lambda a: f"make_float2({ref(a, '.x')}, {ref(a, '.y')})"
         for i in ids:
             op, a, b, c, imm = self.P.ssa[i]
-            if op in ("rnd_bf16", "rnd_f16") and len(lanes) == 2:
-                L.append(f"{ind}  float t{i}_0, t{i}_1; {op}_2({ref(a, '_0')}, {ref(a, '_1')}, t{i}_0, t{i}_1);")
+            if pair and op in ("rnd_bf16", "rnd_f16"):
+                L.append(f"{ind}  float2 t{i}; {op}_2({ref(a, '.x')}, {ref(a, '.y')}, t{i}.x, t{i}.y);")
                 continue
+            if pair and op in ("add", "mul"):
+                L.append(f"{ind}  const float2 t{i} = __f{op}2_rn({both(a)}, {both(b)});")
+                continue
+            if pair and op == "sub":
+                L.append(f"{ind}  const float2 t{i} = __ffma2_rn({both(b)}, make_float2(-1.f, -1.f), {both(a)});")
+                continue
+            exprs = []
             for suf, e in lanes:
                 if op == "leaf":
-                    expr = leafref(imm, e)
+                    exprs.append(leafref(imm, e))
                 elif op == "const":
-                    expr = f"__uint_as_float(0x{imm:08x}u)"
+                    exprs.append(f"__uint_as_float(0x{imm:08x}u)")
                 elif op == "pred":
-                    expr = predref(imm)
+                    exprs.append(predref(imm))
                 else:
-                    expr = _EXPR[op].format(a=ref(a, suf), b=ref(b, suf), c=ref(c, suf))
-                L.append(f"{ind}  const float t{i}{suf} = {expr};")
+                    exprs.append(_EXPR[op].format(a=ref(a, suf), b=ref(b, suf), c=ref(c, suf)))
+            if pair:
+                L.append(f"{ind}  const float2 t{i} = make_float2({exprs[0]}, {exprs[1]});")
+            else:
+                L.append(f"{ind}  const float t{i} = {exprs[0]};")
         for suf, e in lanes:
             L.extend(f"{ind}  {line}" for line in tail(suf, e))
         L.append(f"{ind}}}")
