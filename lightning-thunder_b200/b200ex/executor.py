@@ -1231,6 +1231,7 @@ class B200Region:
 
         absorbed: set[int] = set()
         macro_steps: dict[int, tuple] = {}  # id(bsym) -> (step, input names, output names)
+        self._colsum_sources: set[str] = set()  # values some b200k_colsum step of this region reduces
         # uniform_philox tensors that only feed pointwise work of this region are not launched at all: they become
         # "generated" leaves of the consuming programs, produced in registers by the specialised kernels (and
         # materialised by PwLaunch when a launch cannot use one).  name -> (shape, dtype, lo, hi, seed, offset)
@@ -1432,6 +1433,8 @@ class B200Region:
             if self._single_consumer(up.output.name, consumers, region_outs) is b:
                 absorbed.add(id(up))
             src_name, out_name = self._resolve(up.args[0].name), down.output.name
+
+        self._colsum_sources.add(src_name)
 
         def run(env):
             ready = env.pop(("dbias", src_name), None)
@@ -1643,7 +1646,7 @@ class B200Region:
         specs = compile_chain(inputs, nodes, outs, {n: (g[2], g[3]) for n, g in gen.items()})
         steps = []
         for spec in specs:
-            native = _native_for(spec) if not gen else None
+            native = _native_for(spec, self._colsum_sources) if not gen else None
             if native is not None:
                 steps.append(native)
                 continue
@@ -1669,7 +1672,7 @@ class B200Region:
 from ._signatures import NATIVE_SIGNATURES as _NATIVE_SIGNATURES  # noqa: E402
 
 
-def _native_for(spec) -> _Step | None:
+def _native_for(spec, colsum_sources=frozenset()) -> _Step | None:
     entry = _NATIVE_SIGNATURES.get(spec.signature)
     if entry is None:
         return None
@@ -1705,10 +1708,14 @@ def _native_for(spec) -> _Step | None:
     if kind in ("gelu_bwd", "relu_bwd"):
         act = "gelu" if "gelu" in kind else "relu"
 
+        # the column sums are only worth their scratch buffer and fold launch when a b200k_colsum step of this region
+        # consumes them (a bias gradient); an activation without a bias does not pay for them
+        want_dbias = len(shape) >= 2 and role_out["dx"] in colsum_sources
+
         def run(env):
             # `a` is the saved pre-activation; the bias gradient is the column sum of dx, deposited for the region's
             # b200k_colsum step so that it does not have to re-read dx
-            dx, db = ops.bias_act_bwd(env[role_in["a"]], None, env[role_in["g"]], act, want_dbias=len(shape) >= 2)
+            dx, db = ops.bias_act_bwd(env[role_in["a"]], None, env[role_in["g"]], act, want_dbias=want_dbias)
             env[role_out["dx"]] = dx
             if db is not None:
                 env[("dbias", role_out["dx"])] = db

@@ -944,6 +944,11 @@ class _Gen:
         self.P, self.modes, self.W = P, modes, P.W
         self.vd = len(P.ext) - 1
         self.L: list = []
+        # packed fp32x2 arithmetic (FADD2 / FMUL2 / FFMA2) halves the issue slots of add / sub / mul but wants aligned
+        # register pairs.  Measured: it pays in kernels with registers to spare (RoPE forward 53.2 -> 51.2 us, LayerNorm
+        # forward 35.8 -> 32.3 us) and costs occupancy in the big ones (RoPE backward 67.5 -> 69.8 us, double-buffered
+        # row backwards +2..6 %), so those keep scalar arithmetic.
+        self.packed_math = len(P.leaves) <= 12
 
     def head(self, n_in):
         return _HEAD % {"MAX_RANK": MAX_RANK, "NIN": max(n_in, 1), "NOUT": max(len(self.P.outputs), 1)}
@@ -980,6 +985,7 @@ class _Gen:
         once (`cvt.rn.bf16x2`), everything else runs per lane.  ref(a, lane) names an operand (lane ".x" / ".y" / ""),
         leafref(k, e) reads element e of leaf k, tail(lane, e) -> extra lines per element (stores, partial sums)."""
         pair = W >= 2
+        packed = pair and self.packed_math  # float2 pairs cost registers: only where the kernel has them to spare
         lanes = [(".x", "e"), (".y", "e + 1")] if pair else [("", "e")]
         L.append(f"{ind}#pragma unroll")
         L.append(f"{ind}for (int e = 0; e < {W}; e += {len(lanes)}) {{")
@@ -989,10 +995,10 @@ class _Gen:
             if pair and op in ("rnd_bf16", "rnd_f16"):
                 L.append(f"{ind}  float2 t{i}; {op}_2({ref(a, '.x')}, {ref(a, '.y')}, t{i}.x, t{i}.y);")
                 continue
-            if pair and op in ("add", "mul"):
+            if packed and op in ("add", "mul"):
                 L.append(f"{ind}  const float2 t{i} = __f{op}2_rn({both(a)}, {both(b)});")
                 continue
-            if pair and op == "sub":
+            if packed and op == "sub":
                 L.append(f"{ind}  const float2 t{i} = __ffma2_rn({both(b)}, make_float2(-1.f, -1.f), {both(a)});")
                 continue
             exprs = []
@@ -1329,6 +1335,7 @@ def generate_row(P: Program, modes: tuple) -> str:
     # a two-operand single-reduction row (RMSNorm forward) is already at the HBM limit without it
     worth = len(per_row) >= 3 or bool(cols) or nph >= 3
     nbuf = 2 if (worth and 2 * cost + fixed <= 150 and os.environ.get("B200EX_ROW_PREFETCH", "1") != "0") else 1
+    G.packed_math = nbuf == 1
 
     names_i = lambda b: [f"xo{b}[{k}]" for k in range(no)] + [f"xi[c][{k - no}]" for k in range(no, nv)]
     names_r = lambda b: [f"xo{b}[{k}]" for k in range(no)] + ["0"] * n_inner
