@@ -1648,7 +1648,19 @@ class B200Region:
         for spec in specs:
             native = _native_for(spec, self._colsum_sources) if not gen else None
             if native is not None:
-                steps.append(native)
+                # The family kernels take dense operands.  Strided ones (the two halves of a fused gate/up projection,
+                # a permuted view) are not copied to make them dense: that launch runs the program's generated kernel,
+                # which reads them in place.
+                generic = PwLaunch(spec, {})
+                names = [leaf for leaf, _ in spec.leaves]
+
+                def run(env, native=native, generic=generic, names=names):
+                    if all(env[n].is_contiguous() for n in names):
+                        native.run(env)
+                    else:
+                        env.update(generic.run(env))
+
+                steps.append(_Step(native.kind, run))
                 continue
             launch = PwLaunch(spec, {n: g for n, g in gen.items() if any(n == leaf for leaf, _ in spec.leaves)})
 

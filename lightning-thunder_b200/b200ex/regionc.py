@@ -32,6 +32,7 @@ import ctypes
 import hashlib
 import math
 import os
+import struct
 import threading
 from dataclasses import dataclass, field
 
@@ -831,6 +832,18 @@ __device__ __forceinline__ float rnd_bf16(float x) { return __uint_as_float(f2bf
 __device__ __forceinline__ float rnd_f16(float x) { return h2f(f2h2(x, 0.f) & 0xffffu); }
 __device__ __forceinline__ void rnd_bf16_2(float a, float b, float& x, float& y) { const u32 p = f2bf2(a, b); x = __uint_as_float(p << 16); y = __uint_as_float(p & 0xffff0000u); }
 __device__ __forceinline__ void rnd_f16_2(float a, float b, float& x, float& y) { const u32 p = f2h2(a, b); x = h2f(p & 0xffffu); y = h2f(p >> 16); }
+// packed 16-bit arithmetic on raw words (two bf16 / f16 values per register).  mul/add/sub with an explicit .rn are
+// never contracted into an fma, so each is exactly one rounding of the exact result.
+__device__ __forceinline__ u32 hmul2_bf16(u32 a, u32 b) { u32 d; asm("mul.rn.bf16x2 %%0, %%1, %%2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ u32 hadd2_bf16(u32 a, u32 b) { u32 d; asm("add.rn.bf16x2 %%0, %%1, %%2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ u32 hsub2_bf16(u32 a, u32 b) { u32 d; asm("sub.rn.bf16x2 %%0, %%1, %%2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ u32 hmul2_f16(u32 a, u32 b) { u32 d; asm("mul.rn.f16x2 %%0, %%1, %%2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ u32 hadd2_f16(u32 a, u32 b) { u32 d; asm("add.rn.f16x2 %%0, %%1, %%2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ u32 hsub2_f16(u32 a, u32 b) { u32 d; asm("sub.rn.f16x2 %%0, %%1, %%2;" : "=r"(d) : "r"(a), "r"(b)); return d; }
+__device__ __forceinline__ u32 hneg2(u32 a) { return a ^ 0x80008000u; }
+__device__ __forceinline__ float2 unpk_bf16(u32 w) { return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)); }
+__device__ __forceinline__ float2 unpk_f16(u32 w) { return make_float2(h2f(w & 0xffffu), h2f(w >> 16)); }
+__device__ __forceinline__ u32 wsel(const V4& v, int p) { return p == 0 ? v.x : (p == 1 ? v.y : (p == 2 ? v.z : v.w)); }
 __device__ __forceinline__ float nanmax(float a, float b) { return (a != a || b != b) ? __int_as_float(0x7fc00000) : fmaxf(a, b); }
 __device__ __forceinline__ float nanmin(float a, float b) { return (a != a || b != b) ? __int_as_float(0x7fc00000) : fminf(a, b); }
 __device__ __forceinline__ float sgn(float a) { return a > 0.f ? 1.f : (a < 0.f ? -1.f : a); }
@@ -1019,6 +1032,125 @@ class _Gen:
             L.extend(f"{ind}  {line}" for line in tail(suf, e))
         L.append(f"{ind}}}")
 
+    def emit_pairs16(self, L, ind, live, res, fits, dt, rawleaf, floatleaf, predref, outs):
+        """Element loop of a flat kernel whose 16-bit values stay PACKED (two per 32-bit register) wherever the program
+        allows.  thunder's 16-bit traces round after every op, so `rnd(a * b)`, `rnd(a + b)`, `rnd(a - b)` with a and b
+        already representable in the format are ONE packed instruction on the raw words (`mul/add/sub.rn.bf16x2`): the
+        fp32 result of such an op is exact (or differs from the exact one far below the format's rounding point), so one
+        rounding of the exact result is what upcast-operate-round gives, bit for bit — without unpacking the operands
+        or converting the result.  Negation flips two sign bits, a `where` on a uniform condition selects a word,
+        outputs are stored from the words.  Everything else is computed per lane in fp32 as in emit_elements.
+
+        dt: "bf16" | "f16"; rawleaf(k) -> V4 expression of leaf k's 8 packed elements or None; floatleaf(k, e) -> fp32
+        element expression for leaves that are not packed; outs: [(kind "h"|"f", target array name, ssa id)]."""
+        P = self.P
+        ids = sorted(live)
+        users: dict = {}
+        R = lambda a: res[a]
+        for i in ids:
+            for x in P.ssa[i][1:4]:
+                if x >= 0 and R(x)[0] == "v":
+                    users.setdefault(R(x)[1], []).append(i)
+        out_ids = {R(sid)[1] for _, _, sid in outs if R(sid)[0] == "v"}
+        rnd = "rnd_" + dt
+        hop = {"mul": f"hmul2_{dt}", "add": f"hadd2_{dt}", "sub": f"hsub2_{dt}"}
+
+        def fits16(a):
+            r = R(a)
+            if r[0] == "k":
+                f = struct.unpack("<f", struct.pack("<I", r[1]))[0]
+                return f == f and float(torch.tensor(f, dtype=torch.bfloat16 if dt == "bf16" else torch.float16)) == f
+            return dt in fits[r[1]]
+
+        # mul / add / sub that only feed a rounding to dt and whose operands are exact in dt: absorbed by that rounding
+        absorbed = set()
+        for i in ids:
+            op, a, b = P.ssa[i][0], P.ssa[i][1], P.ssa[i][2]
+            if op in hop and i not in out_ids and users.get(i) and all(P.ssa[u][0] == rnd for u in users[i]) and fits16(a) and fits16(b):
+                absorbed.add(i)
+        L.append(f"{ind}#pragma unroll")
+        L.append(f"{ind}for (int p = 0; p < 4; ++p) {{")
+        hname, fname = {}, {}
+        body: list = []
+
+        def lit16(bits):
+            f = struct.unpack("<f", struct.pack("<I", bits))[0]
+            h = int(torch.tensor(f, dtype=torch.bfloat16 if dt == "bf16" else torch.float16).view(torch.int16)) & 0xFFFF
+            return f"0x{h | (h << 16):08x}u"
+
+        def H(a):  # packed word holding value a for this pair
+            r = R(a)
+            if r[0] == "k":
+                return lit16(r[1])
+            i = r[1]
+            if i not in hname:
+                pack = "f2bf2" if dt == "bf16" else "f2h2"
+                body.append(f"const u32 h{i} = {pack}({F(a)}.x, {F(a)}.y);")  # exact: the value fits the format
+                hname[i] = f"h{i}"
+            return hname[i]
+
+        def F(a):  # float2 holding value a for this pair
+            r = R(a)
+            if r[0] == "k":
+                return f"make_float2(__uint_as_float(0x{r[1]:08x}u), __uint_as_float(0x{r[1]:08x}u))"
+            i = r[1]
+            if i not in fname:
+                body.append(f"const float2 t{i} = unpk_{dt}({hname[i]});")
+                fname[i] = f"t{i}"
+            return fname[i]
+
+        for i in ids:
+            op, a, b, c, imm = P.ssa[i]
+            if i in absorbed:
+                continue
+            if op == "leaf":
+                raw = rawleaf(imm)
+                if raw is not None:
+                    body.append(f"const u32 h{i} = wsel({raw}, p);")
+                    hname[i] = f"h{i}"
+                else:
+                    body.append(f"const float2 t{i} = make_float2({floatleaf(imm, '2 * p')}, {floatleaf(imm, '2 * p + 1')});")
+                    fname[i] = f"t{i}"
+            elif op == "const":
+                continue  # literals are materialised where they are used
+            elif op == "pred":
+                body.append(f"const float2 t{i} = make_float2({predref(imm)}, {predref(imm)});")
+                fname[i] = f"t{i}"
+            elif op == rnd:
+                src = R(a)
+                if src[0] == "v" and src[1] in absorbed:
+                    sop, sa, sb = P.ssa[src[1]][0], P.ssa[src[1]][1], P.ssa[src[1]][2]
+                    body.append(f"const u32 h{i} = {hop[sop]}({H(sa)}, {H(sb)});")
+                else:
+                    pack = "f2bf2" if dt == "bf16" else "f2h2"
+                    fa = F(a)
+                    body.append(f"const u32 h{i} = {pack}({fa}.x, {fa}.y);")
+                hname[i] = f"h{i}"
+            elif op == "neg" and fits16(a) and (R(a)[0] == "k" or R(a)[1] in hname):
+                body.append(f"const u32 h{i} = hneg2({H(a)});")
+                hname[i] = f"h{i}"
+            elif op == "where" and R(a)[0] == "v" and P.ssa[R(a)[1]][0] == "pred" and fits16(b) and fits16(c):
+                body.append(f"const u32 h{i} = {predref(P.ssa[R(a)[1]][4])} != 0.f ? {H(b)} : {H(c)};")
+                hname[i] = f"h{i}"
+            else:
+                if self.packed_math and op in ("add", "mul"):
+                    body.append(f"const float2 t{i} = __f{op}2_rn({F(a)}, {F(b)});")
+                elif self.packed_math and op == "sub":
+                    body.append(f"const float2 t{i} = __ffma2_rn({F(b)}, make_float2(-1.f, -1.f), {F(a)});")
+                else:
+                    fa, fb, fc = (F(x) if x >= 0 else None for x in (a, b, c))
+                    lane = lambda s_: _EXPR[op].format(a=f"{fa}{s_}" if fa else "", b=f"{fb}{s_}" if fb else "", c=f"{fc}{s_}" if fc else "")
+                    body.append(f"const float2 t{i} = make_float2({lane('.x')}, {lane('.y')});")
+                fname[i] = f"t{i}"
+        for kind, target, sid in outs:
+            if kind == "h":
+                body.append(f"{target}[p] = {H(sid)};")
+            else:
+                fs = F(sid)
+                body.append(f"{target}[2 * p] = {fs}.x; {target}[2 * p + 1] = {fs}.y;")
+        L.extend(f"{ind}  {line}" for line in body)
+        L.append(f"{ind}}}")
+
     def ssa_line(self, i, ref, leafref, predref):
         op, a, b, c, imm = self.P.ssa[i]
         if op == "leaf":
@@ -1149,6 +1281,7 @@ def _fold(P: Program, assume: dict):
         elif op == "leaf":
             undecided.update(ci for ci in P.leaves[imm].guard if ci not in assume)
         stack.extend(x for x in (a, b, c) if x >= 0)
+    _fold.last_fits = fits  # per-value set of 16-bit formats the value is exactly representable in (for this call)
     return res, live, undecided
 
 
@@ -1209,7 +1342,29 @@ def generate_flat(P: Program, modes: tuple, unroll: int, min_ctas: int = 0) -> s
             return f"{ind}{{ const float b = ld1_{dt}({ptr}, {off}); for (int e = 0; e < {W}; ++e) {dst}[e] = b; }}"
         return f"{ind}{{ const i64 o = {off}, es = {G.leaf_estride(k)}; for (int e = 0; e < {W}; ++e) {dst}[e] = ld1_{dt}({ptr}, o + e * es); }}"
 
-    def math_and_store(res, live, ind, leafref):
+    # 16-bit values stay packed when the kernel works on one 16-bit format with full 16-byte items (emit_pairs16)
+    sixteen = {modes[k][1] for k in range(len(P.leaves)) if modes[k][1] in ("bf16", "f16")} | {_DT[o.dtype] for o in P.outputs if _DT[o.dtype] in ("bf16", "f16")}
+    dt16 = next(iter(sixteen)) if (len(sixteen) == 1 and W == 8 and os.environ.get("B200EX_PACKED16", "1") != "0") else None
+    is_raw = lambda k: dt16 is not None and modes[k][0] == "v" and modes[k][1] == dt16
+
+    def math_and_store(res, live, ind, leafref, rawref):
+        if dt16 is not None:
+            outs = []
+            for k, o in enumerate(P.outputs):
+                if _DT[o.dtype] == dt16:
+                    L.append(f"{ind}u32 ow{k}[4];")
+                    outs.append(("h", f"ow{k}", o.sid))
+                else:
+                    L.append(f"{ind}float o{k}[{W}];")
+                    outs.append(("f", f"o{k}", o.sid))
+            G.emit_pairs16(L, ind, live, res, _fold.last_fits, dt16, lambda k: rawref(k) if is_raw(k) else None, leafref,
+                           lambda ci: f"(cn[u][{ci}] ? 1.f : 0.f)", outs)
+            for k, o in enumerate(P.outputs):
+                if _DT[o.dtype] == dt16:
+                    L.append(f"{ind}stg16((u16*)P.out[{k}].ptr + {out_off}, V4{{ow{k}[0], ow{k}[1], ow{k}[2], ow{k}[3]}});")
+                else:
+                    L.append(f"{ind}stv_{_DT[o.dtype]}<{W}>(P.out[{k}].ptr, {out_off}, o{k});")
+            return
         for k in range(len(P.outputs)):
             L.append(f"{ind}float o{k}[{W}];")
 
@@ -1222,35 +1377,48 @@ def generate_flat(P: Program, modes: tuple, unroll: int, min_ctas: int = 0) -> s
         for k, o in enumerate(P.outputs):
             L.append(f"{ind}stv_{_DT[o.dtype]}<{W}>(P.out[{k}].ptr, {out_off}, o{k});")
 
+    def load_raw(k, ind, dst):
+        return f"{ind}{dst} = ldg16((const u16*)P.in[{G.slot[k]}].ptr + {G.leaf_offset(k, inames)});"
+
     if not und0:
         # one straight-line block: all loads of all U items first (every request in flight), then math and stores
         res, live, _ = _fold(P, {})
+        fits0 = _fold.last_fits
         used = sorted(P.ssa[i][4] for i in live if P.ssa[i][0] == "leaf")
-        if used:
+        if any(not is_raw(k) for k in used):
             L.append(f"    float v[{U}][{len(P.leaves)}][{W}];")
+        if any(is_raw(k) for k in used):
+            L.append(f"    V4 rw[{U}][{len(P.leaves)}];")
         L.append("    #pragma unroll")
         L.append(f"    for (int u = 0; u < {U}; ++u) if (live[u]) {{")
         for k in used:
-            L.append(load(k, "      ", f"v[u][{k}]"))
+            L.append(load_raw(k, "      ", f"rw[u][{k}]") if is_raw(k) else load(k, "      ", f"v[u][{k}]"))
         L.append("    }")
         L.append("    #pragma unroll")
         L.append(f"    for (int u = 0; u < {U}; ++u) if (live[u]) {{")
-        math_and_store(res, live, "      ", lambda k, e: f"v[u][{k}][{e}]")
+        _fold.last_fits = fits0
+        math_and_store(res, live, "      ", lambda k, e: f"v[u][{k}][{e}]", lambda k: f"rw[u][{k}]")
         L.append("    }")
     else:
         blocks = [0]
 
         def tree(assume, ind):
             res, live, und = _fold(P, assume)
+            fits_here = _fold.last_fits
             if not und:
                 blocks[0] += 1
                 if blocks[0] > MAX_BLOCKS:
                     raise PwUnsupported("too many condition combinations for one kernel")
                 L.append(f"{ind}{{")
                 for k in sorted(P.ssa[i][4] for i in live if P.ssa[i][0] == "leaf"):
-                    L.append(f"{ind}  float v{k}[{W}];")
-                    L.append(load(k, ind + "  ", f"v{k}"))
-                math_and_store(res, live, ind + "  ", lambda k, e: f"v{k}[{e}]")
+                    if is_raw(k):
+                        L.append(f"{ind}  V4 r{k};")
+                        L.append(load_raw(k, ind + "  ", f"r{k}"))
+                    else:
+                        L.append(f"{ind}  float v{k}[{W}];")
+                        L.append(load(k, ind + "  ", f"v{k}"))
+                _fold.last_fits = fits_here
+                math_and_store(res, live, ind + "  ", lambda k, e: f"v{k}[{e}]", lambda k: f"r{k}")
                 L.append(f"{ind}}}")
                 return
             ci = min(und)

@@ -408,3 +408,24 @@ def test_reference_bart_self_attention():
     err = (results["b200"][0].float() - results["torch"][0].float()).norm() / results["torch"][0].float().norm()
     assert err.item() < 1e-2
     _grads_close(results, zero_in_exact_arithmetic=("k_proj.bias",))
+
+
+def test_strided_operands_of_a_family_region_are_read_in_place():
+    """SwiGLU on the two halves of a fused gate/up projection (`x.chunk(2, -1)`: row stride 2*I): the region still is the
+    SwiGLU family, but the launch goes to the program's generated kernel, which reads the strided halves in place —
+    no dense copy (ops.COPY_STATS stays put), same bits as the dense route."""
+    from b200ex import ops
+
+    g = torch.Generator(device=DEV).manual_seed(5)
+    gu = (torch.randn(256, 2 * 1024, generator=g, device=DEV) * 2).to(BF)
+    fn = lambda a, b: F.silu(a) * b
+    jf = thunder.jit(fn, executors=[b200.ex])
+    a, b = gu.chunk(2, -1)
+    assert not a.is_contiguous()
+    before = dict(ops.COPY_STATS)
+    got = jf(a, b)
+    assert ops.COPY_STATS == before, "a strided operand was copied"
+    dense = jf(a.contiguous(), b.contiguous())
+    assert [k for _, ks in fusions(thunder.last_traces(jf)[-1]) for k in ks] == ["b200k_swiglu_fwd"]
+    assert torch.equal(got, dense)
+    assert torch.equal(got, thunder.jit(fn, executors=["torch"])(a, b))
