@@ -1809,6 +1809,12 @@ class _Kernel:
         self.launches += 1
 
 
+# Resident CTAs (256 threads) per SM a gather kernel's grid is sized for.  Measured on the RoPE forward (7 loads + 3
+# stores of 16 bytes per thread, 32 registers): 8 CTAs per SM 59.3 us, 6 -> 51.3 us, 5 -> 53.2 us, 4 -> 57.1 us — past
+# 1536 threads per SM the extra requests in flight only lengthen the DRAM queues (profiles/r2_bench_regionc.txt).
+_GRID_CTAS = int(os.environ.get("B200EX_FLAT_GRIDCTAS", "6"))
+
+
 def flat_unroll(P: Program) -> int:
     """Work items per thread and trip of a flat kernel.  Several only for straight-line programs (all loads of all
     items are issued first); a program with `cat` / `pad` branches takes one item at a time."""
@@ -1919,7 +1925,7 @@ class RegionLaunch:
             if P.kind == "flat":
                 U = flat_unroll(P)
                 items = math.prod(P.ext) // P.W
-                geo = (max(1, min((items + 256 * U - 1) // (256 * U), sms * kernel.ctas_per_sm(256))), 256, 0, 0)
+                geo = (max(1, min((items + 256 * U - 1) // (256 * U), sms * min(_GRID_CTAS, kernel.ctas_per_sm(256)))), 256, 0, 0)
             else:
                 T, C, RPC, block = row_geometry(P)
                 ncol = sum(1 for o in P.outputs if o.kind == "col")

@@ -77,6 +77,7 @@ struct Vec<float> {
     __device__ static __forceinline__ uint4 pack2(const float2* f) {
         return make_uint4(__float_as_uint(f[0].x), __float_as_uint(f[0].y), __float_as_uint(f[1].x), __float_as_uint(f[1].y));
     }
+    __device__ static __forceinline__ uint32_t pack_word(float2 x) { return __float_as_uint(x.x); }  // never executed
     __device__ static __forceinline__ float2 rnd2f(float2 x) { return x; }
     __device__ static __forceinline__ float load1(const void* p, int64_t i) { return reinterpret_cast<const float*>(p)[i]; }
     __device__ static __forceinline__ void store1(void* p, int64_t i, float x) { reinterpret_cast<float*>(p)[i] = x; }
@@ -163,6 +164,10 @@ struct Vec<__half> {
         const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i) f[i] = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+    }
+    __device__ static __forceinline__ uint32_t pack_word(float2 x) {
+        __half2 p = __floats2half2_rn(x.x, x.y);
+        return *reinterpret_cast<uint32_t*>(&p);
     }
     __device__ static __forceinline__ uint4 pack2(const float2* f) {
         uint32_t w[4];

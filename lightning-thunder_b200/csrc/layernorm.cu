@@ -11,6 +11,8 @@
 // launched with programmatic stream serialization.
 #include <cstdlib>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace b200k {
@@ -229,6 +231,7 @@ layernorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ x, cons
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     const float2 hid2 = make_float2(-hidden_f, -hidden_f), rcp2 = make_float2(1.0f / hidden_f, 1.0f / hidden_f);
+    const bool hidden_pow2 = (__float_as_uint(hidden_f) & 0x007fffffu) == 0u;  // mantissa bits all zero
     float rs_next[kRows], mu_next[kRows];
     auto load_stats = [&](int64_t g) {
 #pragma unroll
@@ -283,11 +286,13 @@ layernorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ x, cons
                 for (int e = 0; e < kP; ++e) {
                     const float2 gw = kHasW ? __fmul2_rn(wf[i][e], dyf[e]) : dyf[e];
                     a1 = __ffma2_rn(__fadd2_rn(xf[e], mu2), gw, a1);
-                    a2 = __fadd2_rn(a2, __fmul2_rn(rstd2, gw));
+                    a2 = __fadd2_rn(a2, gw);
                 }
             }
+            // rstd is a row constant: it multiplies the sum once instead of every term (the sum is reassociated
+            // across lanes anyway, so this is within the same fp32 rounding noise)
             c[2 * r] = warp_reduce(a1.x + a1.y, SumOp{});
-            c[2 * r + 1] = warp_reduce(a2.x + a2.y, SumOp{});
+            c[2 * r + 1] = warp_reduce((a2.x + a2.y) * rs[r], SumOp{});
         }
         if (ncw > 1) {
             float* rb = red + parity * (2 * kRows * 32);
@@ -317,35 +322,47 @@ layernorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ x, cons
             phase ^= 1u;
         }
 
+        // A power-of-two row width divides exactly by one multiplication (its reciprocal is exact and the product
+        // is the correctly rounded quotient, subnormals included); other widths take the corrected division.
+        auto emit = [&](auto pow2_tag) {
+            constexpr bool kPow2 = decltype(pow2_tag)::value;
 #pragma unroll
-        for (int r = 0; r < kRows; ++r) {
-            const int64_t row = row0 + r;
-            if (row >= rows) break;
-            const float rstd_r = rs[r];
-            // var_mean's vjp in the reference's order: gvar = (-0.5 * c1) * rstd^3, mean_grad = (1/H) * c2,
-            // var_grad = ((2 * gvar) * (x - mean)) / H
-            const float gvar2 = 2.f * ((-0.5f * c[2 * r]) * (rstd_r * rstd_r * rstd_r));
-            const float mg = inv_hidden * -c[2 * r + 1];
-            const float2 mu2 = make_float2(-mu[r], -mu[r]), rstd2 = make_float2(rstd_r, rstd_r);
-            const float2 gv2 = make_float2(gvar2, gvar2), mg2 = make_float2(mg, mg);
+            for (int r = 0; r < kRows; ++r) {
+                const int64_t row = row0 + r;
+                if (row >= rows) break;
+                const float rstd_r = rs[r];
+                // var_mean's vjp in the reference's order: gvar = (-0.5 * c1) * rstd^3, mean_grad = (1/H) * c2,
+                // var_grad = ((2 * gvar) * (x - mean)) / H
+                const float gvar2 = 2.f * ((-0.5f * c[2 * r]) * (rstd_r * rstd_r * rstd_r));
+                const float mg = inv_hidden * -c[2 * r + 1];
+                const float2 mu2 = make_float2(-mu[r], -mu[r]), rstd2 = make_float2(rstd_r, rstd_r);
+                const float2 gv2 = make_float2(gvar2, gvar2), mg2 = make_float2(mg, mg);
 #pragma unroll
-            for (int i = 0; i < kVpl; ++i) {
-                float2 dyf[kP], xf[kP], o[kP];
-                V::unpack2(dyv[r][i], dyf);
-                V::unpack2(xv[r][i], xf);
+                for (int i = 0; i < kVpl; ++i) {
+                    float2 dyf[kP], xf[kP], o[kP];
+                    uint32_t ow[4] = {0u, 0u, 0u, 0u};
+                    V::unpack2(dyv[r][i], dyf);
+                    V::unpack2(xv[r][i], xf);
 #pragma unroll
-                for (int e = 0; e < kP; ++e) {
-                    const float2 gw = kHasW ? __fmul2_rn(wf[i][e], dyf[e]) : dyf[e];
-                    const float2 xc = __fadd2_rn(xf[e], mu2);
-                    const float2 direct = __fmul2_rn(rstd2, gw);
-                    const float2 stats = __fadd2_rn(mg2, div_by_const2(__fmul2_rn(gv2, xc), hid2, rcp2));
-                    o[e] = kIsF32 ? __fadd2_rn(direct, stats) : __fadd2_rn(V::rnd2f(direct), V::rnd2f(stats));
-                    if constexpr (kHasW) dwacc[i][e] = __fadd2_rn(dwacc[i][e], V::rnd2f(__fmul2_rn(__fmul2_rn(xc, rstd2), dyf[e])));
-                    if constexpr (kHasB) dbacc[i][e] = __fadd2_rn(dbacc[i][e], dyf[e]);
+                    for (int e = 0; e < kP; ++e) {
+                        const float2 gw = kHasW ? __fmul2_rn(wf[i][e], dyf[e]) : dyf[e];
+                        const float2 xc = __fadd2_rn(xf[e], mu2);
+                        const float2 direct = __fmul2_rn(rstd2, gw);
+                        const float2 t = __fmul2_rn(gv2, xc);
+                        const float2 stats = __fadd2_rn(mg2, kPow2 ? __fmul2_rn(t, rcp2) : div_by_const2(t, hid2, rcp2));
+                        // 16-bit: round(round(direct) + round(stats)) as two packed converts and one packed add — the
+                        // packed add rounds the exact sum once, which equals the fp32 add followed by the rounding
+                        if constexpr (kIsF32) o[e] = __fadd2_rn(direct, stats);
+                        else ow[e] = Pk<T>::add(V::pack_word(direct), V::pack_word(stats));
+                        if constexpr (kHasW) dwacc[i][e] = __fadd2_rn(dwacc[i][e], V::rnd2f(__fmul2_rn(__fmul2_rn(xc, rstd2), dyf[e])));
+                        if constexpr (kHasB) dbacc[i][e] = __fadd2_rn(dbacc[i][e], dyf[e]);
+                    }
+                    st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, kIsF32 ? V::pack2(o) : make_uint4(ow[0], ow[1], ow[2], ow[3]));
                 }
-                st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, V::pack2(o));
             }
-        }
+        };
+        if (hidden_pow2) emit(std::true_type{});
+        else emit(std::false_type{});
     }
 
     auto flush = [&](float* partial, float2 (&acc)[kVpl][kP]) {
@@ -621,6 +638,7 @@ int ln_launch_bwd(const void* dy, const void* x, const void* w, const float* mea
     };
     int rc;
     if (vpl == 1) rc = kr == 1 ? go(layernorm_bwd_tma_kernel<T, 1, 1, kHasW, kHasB>) : go(layernorm_bwd_tma_kernel<T, 1, 2, kHasW, kHasB>);
+    else if (vpl == 2 && kr == 1 && t.minb == 2) rc = go(layernorm_bwd_tma_kernel<T, 2, 1, kHasW, kHasB, 256, 2>);
     else if (vpl == 2) rc = kr == 1 ? go(layernorm_bwd_tma_kernel<T, 2, 1, kHasW, kHasB>) : go(layernorm_bwd_tma_kernel<T, 2, 2, kHasW, kHasB>);
     else if (cthreads <= 128 && t.minb == 3) rc = go(layernorm_bwd_tma_kernel<T, 4, 1, kHasW, kHasB, 128, 3>);
     else if (cthreads <= 128 && t.minb == 4) rc = go(layernorm_bwd_tma_kernel<T, 4, 1, kHasW, kHasB, 128, 4>);
