@@ -44,11 +44,12 @@ __device__ __forceinline__ float2 erf2(float2 x) {
         const float2 t = make_float2(hw_rcp(d.x), hw_rcp(d.y));
         const float2 q = __fmul2_rn(__fmul2_rn(ax, ax), f2(-1.4426950408889634f));
         const float2 e = make_float2(hw_ex2(q.x), hw_ex2(q.y));
-        float2 p = __ffma2_rn(f2(1.061405429f), t, f2(-1.453152027f));
-        p = __ffma2_rn(p, t, f2(1.421413741f));
-        p = __ffma2_rn(p, t, f2(-0.284496736f));
-        p = __ffma2_rn(p, t, f2(0.254829592f));
-        const float2 r = __ffma2_rn(__fmul2_rn(p, t), make_float2(-e.x, -e.y), f2(1.0f));
+        // the polynomial carries the minus sign of 1 - p(t) * t * e (negation is exact, so the bits are the same)
+        float2 p = __ffma2_rn(f2(-1.061405429f), t, f2(1.453152027f));
+        p = __ffma2_rn(p, t, f2(-1.421413741f));
+        p = __ffma2_rn(p, t, f2(0.284496736f));
+        p = __ffma2_rn(p, t, f2(-0.254829592f));
+        const float2 r = __ffma2_rn(__fmul2_rn(p, t), e, f2(1.0f));
         return make_float2(copysignf(r.x, x.x), copysignf(r.y, x.y));
     } else {
         return make_float2(erff(x.x), erff(x.y));
@@ -138,28 +139,30 @@ __device__ __forceinline__ uint32_t bf2_mul(uint32_t a, uint32_t b) {
 }
 constexpr uint32_t kBf2Half = 0x3F003F00u;  // (0.5, 0.5)
 
-// erf(z) by Abramowitz-Stegun 7.1.26 as in erf2<true>; also hands back e = exp(-z^2), which the backward's
-// density term needs again.
-__device__ __forceinline__ float2 erf2_with_exp(float2 z, float2& e_out) {
-    const float2 ax = make_float2(fabsf(z.x), fabsf(z.y));
+// erf of the bf16 pair in word zw by Abramowitz-Stegun 7.1.26 as in erf2<true>, rounded to a bf16 pair; also hands
+// back e = exp(-z^2), which the backward's density term needs again.  |z| and the final copysign are one LOP3 each
+// on the packed word (rounding is symmetric in the sign, so copysign-then-round = round-then-copysign).
+__device__ __forceinline__ uint32_t erf_word_with_exp(uint32_t zw, float2& e_out) {
+    using V = Vec<__nv_bfloat16>;
+    const float2 ax = V::word2(zw & 0x7fff7fffu);
     const float2 d = __ffma2_rn(f2(0.3275911f), ax, f2(1.0f));
     const float2 t = make_float2(hw_rcp(d.x), hw_rcp(d.y));
     const float2 q = __fmul2_rn(__fmul2_rn(ax, ax), f2(-1.4426950408889634f));
     const float2 e = make_float2(hw_ex2(q.x), hw_ex2(q.y));
     e_out = e;
-    float2 p = __ffma2_rn(f2(1.061405429f), t, f2(-1.453152027f));
-    p = __ffma2_rn(p, t, f2(1.421413741f));
-    p = __ffma2_rn(p, t, f2(-0.284496736f));
-    p = __ffma2_rn(p, t, f2(0.254829592f));
-    const float2 r = __ffma2_rn(__fmul2_rn(p, t), make_float2(-e.x, -e.y), f2(1.0f));
-    return make_float2(copysignf(r.x, z.x), copysignf(r.y, z.y));
+    float2 p = __ffma2_rn(f2(-1.061405429f), t, f2(1.453152027f));
+    p = __ffma2_rn(p, t, f2(-1.421413741f));
+    p = __ffma2_rn(p, t, f2(0.284496736f));
+    p = __ffma2_rn(p, t, f2(-0.254829592f));
+    const float2 r = __ffma2_rn(__fmul2_rn(p, t), e, f2(1.0f));
+    return (V::pack_word(r) & 0x7fff7fffu) | (zw & 0x80008000u);
 }
 
 // cdf word = 0.5 + 0.5 * erf(a / sqrt2), each step rounded; e_out = exp(-z^2) of the rounded z
 __device__ __forceinline__ uint32_t gelu_cdf_word(uint32_t a2, float2& e_out) {
     using V = Vec<__nv_bfloat16>;
-    const float2 z = V::rnd2f(__fmul2_rn(V::word2(a2), f2(kInvSqrt2)));
-    const uint32_t erf_w = V::pack_word(erf2_with_exp(z, e_out));
+    const uint32_t zw = V::pack_word(__fmul2_rn(V::word2(a2), f2(kInvSqrt2)));
+    const uint32_t erf_w = erf_word_with_exp(zw, e_out);
     return bf2_add(bf2_mul(erf_w, kBf2Half), kBf2Half);
 }
 __device__ __forceinline__ uint32_t gelu_fwd_word(uint32_t a2) {
@@ -189,12 +192,18 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
     const int tid = threadIdx.x, nthr = blockDim.x;
     const int v0 = blockIdx.y * (nthr * kBaVpl) + tid;
     float bf[kBaVpl][kE], acc[kBaVpl][kE];
+    uint4 braw[kBaVpl];  // the bias vectors as loaded (the packed path adds them word by word)
+#pragma unroll
+    for (int i = 0; i < kBaVpl; ++i) braw[i] = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
     for (int i = 0; i < kBaVpl; ++i) {
         const int v = v0 + i * nthr;
 #pragma unroll
         for (int e = 0; e < kE; ++e) bf[i][e] = 0.f, acc[i][e] = 0.f;
-        if (kHasBias && v < nvec) V::unpack(ld_keep(reinterpret_cast<const uint4*>(bias) + v), bf[i]);
+        if (kHasBias && v < nvec) {
+            braw[i] = ld_keep(reinterpret_cast<const uint4*>(bias) + v);
+            V::unpack(braw[i], bf[i]);
+        }
     }
     // software pipeline: the next row's vectors are requested before the current row's ALU chain starts, so
     // every thread always has loads in flight
@@ -219,17 +228,17 @@ bias_act_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __
                 if (v < nvec) {
                     const uint32_t xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w};
                     const uint32_t gw[4] = {gv[i].x, gv[i].y, gv[i].z, gv[i].w};
+                    const uint32_t bw[4] = {braw[i].x, braw[i].y, braw[i].z, braw[i].w};
                     uint32_t aw[4], ow[4];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        // bias was unpacked exactly, so repacking it is exact too
-                        aw[k] = kHasBias ? bf2_add(xw[k], V::pack_word(make_float2(bf[i][2 * k], bf[i][2 * k + 1]))) : xw[k];
+                        aw[k] = kHasBias ? bf2_add(xw[k], bw[k]) : xw[k];
                         if constexpr (kBwd) {
                             ow[k] = gelu_bwd_word(aw[k], gw[k]);
                             if constexpr (kAccum) {
-                                const float2 d = V::word2(ow[k]);
-                                acc[i][2 * k] += d.x;
-                                acc[i][2 * k + 1] += d.y;
+                                const float2 sum = __fadd2_rn(make_float2(acc[i][2 * k], acc[i][2 * k + 1]), V::word2(ow[k]));
+                                acc[i][2 * k] = sum.x;
+                                acc[i][2 * k + 1] = sum.y;
                             }
                         } else {
                             ow[k] = gelu_fwd_word(aw[k]);
