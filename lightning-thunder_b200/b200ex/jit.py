@@ -224,8 +224,8 @@ def compile_cubin(source: str) -> bytes:
 _culaunch = {"fn": None, "tried": False}
 
 
-def fast_launch(driver, func, grid: int, block: int, stream: int, params_addr: int) -> None:
-    """cuLaunchKernel(func, grid, 1, 1, block, 1, 1, 0, stream, {&params}, 0).  Goes straight to libcuda through
+def fast_launch(driver, func, grid: int, block: int, stream: int, params_addr: int, smem: int = 0) -> None:
+    """cuLaunchKernel(func, grid, 1, 1, block, 1, 1, smem, stream, {&params}, 0).  Goes straight to libcuda through
     ctypes — a couple of microseconds — and only falls back to the cuda-python wrapper (ten times that per call, which
     is as long as some of the kernels) when libcuda cannot be opened that way."""
     if not _culaunch["tried"]:
@@ -241,9 +241,9 @@ def fast_launch(driver, func, grid: int, block: int, stream: int, params_addr: i
     argv = (ctypes.c_void_p * 1)(params_addr)
     fn = _culaunch["fn"]
     if fn is not None:
-        err = fn(int(func), grid, 1, 1, block, 1, 1, 0, stream, ctypes.addressof(argv), None)
+        err = fn(int(func), grid, 1, 1, block, 1, 1, smem, stream, ctypes.addressof(argv), None)
     else:
-        (err,) = driver.cuLaunchKernel(func, grid, 1, 1, block, 1, 1, 0, stream, ctypes.addressof(argv), 0)
+        (err,) = driver.cuLaunchKernel(func, grid, 1, 1, block, 1, 1, smem, stream, ctypes.addressof(argv), 0)
     if int(err) != 0:
         raise RuntimeError(f"b200ex jit: cuLaunchKernel failed: {err}")
 

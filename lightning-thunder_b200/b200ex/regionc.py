@@ -821,6 +821,13 @@ struct V2 { u32 x, y; };
 __device__ __forceinline__ V4 ldg16(const void* p) { V4 r; asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%%0,%%1,%%2,%%3}, [%%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p)); return r; }
 __device__ __forceinline__ V2 ldg8(const void* p) { V2 r; asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%%0,%%1}, [%%2];" : "=r"(r.x), "=r"(r.y) : "l"(p)); return r; }
 __device__ __forceinline__ u32 ldg4(const void* p) { u32 r; asm volatile("ld.global.nc.L1::no_allocate.u32 %%0, [%%1];" : "=r"(r) : "l"(p)); return r; }
+// 16-byte asynchronous global -> shared copy (LDGSTS, L2 only); ok == false copies nothing and zero-fills
+__device__ __forceinline__ void cpa16(void* dst, const void* src, bool ok) {
+  const u32 d = (u32)__cvta_generic_to_shared(dst); const int n = ok ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%%0], [%%1], 16, %%2;" :: "r"(d), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cpa_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cpa_wait() { asm volatile("cp.async.wait_group %%0;" :: "n"(N) : "memory"); }
 __device__ __forceinline__ void stg16(void* p, V4 v) { asm volatile("st.global.L1::no_allocate.v4.u32 [%%0], {%%1,%%2,%%3,%%4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory"); }
 __device__ __forceinline__ void stg8(void* p, V2 v) { asm volatile("st.global.L1::no_allocate.v2.u32 [%%0], {%%1,%%2};" :: "l"(p), "r"(v.x), "r"(v.y) : "memory"); }
 __device__ __forceinline__ void stg4(void* p, u32 v) { asm volatile("st.global.L1::no_allocate.u32 [%%0], %%1;" :: "l"(p), "r"(v) : "memory"); }
@@ -1467,7 +1474,60 @@ def row_geometry(P: Program):
     return T, C, block // T, block
 
 
-def generate_row(P: Program, modes: tuple) -> str:
+def _row_operands(P: Program):
+    """(hoisted, per_row, scalars): leaf indices that are row-independent full operands, per-row full operands, and
+    per-row scalars."""
+    no = P.n_outer
+    leaf_sid = _leaf_sids(P)
+
+    def uses_outer(lf):
+        vs = {v for c in lf.coords for v, _ in c[0]} | {v for ci in lf.guard for v, _ in P.conds[ci][0]}
+        return any(v < no for v in vs)
+
+    full_leaves = [k for k in range(len(P.leaves)) if P.full[leaf_sid[k]]]
+    hoisted = [k for k in full_leaves if not uses_outer(P.leaves[k])]
+    per_row = [k for k in full_leaves if k not in hoisted]
+    scalars = [k for k in range(len(P.leaves)) if k not in full_leaves]
+    return hoisted, per_row, scalars
+
+
+_ES = {"bf16": 2, "f16": 2, "f32": 4}
+# B200EX_ROW_RING: "auto" (default: time both builds on the first call), "1" (always the ring), "0" (never)
+_RING_MODE = os.environ.get("B200EX_ROW_RING", "auto")
+
+
+def row_ring(P: Program, modes: tuple):
+    """(stages, 16-byte units per thread and stage, dynamic shared-memory bytes) of the row kernel's staging ring, or
+    (0, 0, 0) when the kernel keeps its rows in registers.
+
+    A row kernel at two 256-thread CTAs per SM that prefetches one row ahead in registers has 2 x 8 KB per operand in
+    flight per SM — a quarter of what HBM3e needs to stay busy (ncu: the LayerNorm forward ran at 2 TB/s with its warps
+    waiting on the loads).  With the ring every thread copies its own chunks of the next stages - 1 rows into its own
+    shared-memory slots (cp.async, 16 bytes each) and reads them back itself, so no barrier is involved and the depth
+    is bounded by shared memory, not registers."""
+    if os.environ.get("B200EX_ROW_RING", "1") == "0" or P.kind != "row":
+        return 0, 0, 0
+    hoisted, per_row, _ = _row_operands(P)
+    T, C, RPC, block = row_geometry(P)
+    cols = sum(1 for o in P.outputs if o.kind == "col")
+    nph = max(P.phase) + 1
+    if not per_row or not (len(per_row) >= 3 or cols or nph >= 3):
+        return 0, 0, 0
+    units = 0
+    for k in per_row:
+        mode, dt = modes[k][0], modes[k][1]
+        if mode != "v" or dt not in _ES or (P.W * _ES[dt]) % 16:
+            return 0, 0, 0
+        units += C * (P.W * _ES[dt] // 16)
+    stage = units * block * 16
+    budget = 200 * 1024 // max(1, 512 // block)
+    nb = min(6, max(3, -(-32 * 1024 // stage) + 1), budget // stage)
+    if nb < 2:
+        return 0, 0, 0
+    return nb, units, nb * stage
+
+
+def generate_row(P: Program, modes: tuple, use_ring: bool = True) -> str:
     """Row-persistent kernel.  One row lives in the registers of T threads (a warp, or a whole CTA), C interleaved
     chunks of W elements per thread.  16-bit operands stay packed (one 16-byte register quad per chunk) and are
     unpacked where they are used, which halves their register cost and pays for a second buffer: the next row's loads
@@ -1503,7 +1563,17 @@ def generate_row(P: Program, modes: tuple) -> str:
     # a two-operand single-reduction row (RMSNorm forward) is already at the HBM limit without it
     worth = len(per_row) >= 3 or bool(cols) or nph >= 3
     nbuf = 2 if (worth and 2 * cost + fixed <= 150 and os.environ.get("B200EX_ROW_PREFETCH", "1") != "0") else 1
-    G.packed_math = nbuf == 1
+    NB, ring_units, _ = row_ring(P, modes) if use_ring else (0, 0, 0)
+    ring = NB > 0
+    if ring:
+        nbuf = 1  # rows wait in shared memory, not in a second set of registers
+        # 16-byte unit of (leaf k, chunk c, part j) inside a stage: unit index * block + threadIdx.x
+        ring_base, ring_n16, u_ = {}, {}, 0
+        for k in per_row:
+            ring_n16[k] = W * _ES[modes[k][1]] // 16
+            ring_base[k] = u_
+            u_ += C * ring_n16[k]
+    G.packed_math = nbuf == 1 and not (ring and len(per_row) + len(hoisted) + len(cols) > 4)
 
     names_i = lambda b: [f"xo{b}[{k}]" for k in range(no)] + [f"xi[c][{k - no}]" for k in range(no, nv)]
     names_r = lambda b: [f"xo{b}[{k}]" for k in range(no)] + ["0"] * n_inner
@@ -1533,6 +1603,8 @@ def generate_row(P: Program, modes: tuple) -> str:
             return f"vh{k}[c][{e}]"
         if k in packed:
             return f"unp_{modes[k][1]}(z{k}, {e})"
+        if ring and k in per_row:
+            return f"zf{k}[{e}]"
         return f"v{b}_{k}[c][{e}]"
 
     # identities known without any condition decided (re-rounding an exact value, x + 0): res[i] names what value i is
@@ -1580,35 +1652,63 @@ def generate_row(P: Program, modes: tuple) -> str:
                 L.append(f"  bool cr{b}_{ci} = false;")
         if "mixed" in cond_cls:
             L.append(f"  bool cm{b}_[C_][{len(P.conds)}];")
-        for k in per_row:
-            L.append(f"  V4 w{b}_{k}[C_];" if k in packed else f"  float v{b}_{k}[C_][W_];")
+        if not ring:
+            for k in per_row:
+                L.append(f"  V4 w{b}_{k}[C_];" if k in packed else f"  float v{b}_{k}[C_][W_];")
         for k in scalars:
             L.append(f"  float s{b}_{k} = 0.f;")
-
-    def emit_load(b, rowvar, ind):
-        L.append(f"{ind}{{ i64 r = {rowvar};")
-        for k in range(no - 1, -1, -1):
-            if k == 0:
-                L.append(f"{ind}  xo{b}[0] = (int)r;")
-            else:
-                L.append(f"{ind}  xo{b}[{k}] = (int)(r % {ext[k]}); r /= {ext[k]};")
-        L.append(f"{ind}}}")
+    if ring:
+        L.append("  extern __shared__ __align__(16) V4 ring_[];")
+        L.append(f"  int xo1[{max(no, 1)}];  // coordinates of a row being prefetched")
         for ci, cls in enumerate(cond_cls):
             if cls == "outer":
-                L.append(f"{ind}cr{b}_{ci} = {G.cond_expr(ci, names_r(b))};")
+                L.append(f"  bool cr1_{ci} = false;")
         if "mixed" in cond_cls:
-            L.append(f"{ind}#pragma unroll")
-            L.append(f"{ind}for (int c = 0; c < C_; ++c) {{")
-            for ci, cls in enumerate(cond_cls):
-                if cls == "mixed":
-                    L.append(f"{ind}  cm{b}_[c][{ci}] = {G.cond_expr(ci, names_i(b))};")
-            L.append(f"{ind}}}")
+            L.append(f"  bool cm1_[C_][{len(P.conds)}];")
         for k in scalars:
+            L.append(f"  float s1_{k} = 0.f;  // the next row's")
+
+    def emit_load(b, rowvar, ind, coords=True, scal=True, full=True, slot=None):
+        """coords: the row's outer coordinates and conditions into set b; scal: its scalars; full: its operands — into
+        registers, or (slot given) into ring stage `slot` with cp.async."""
+        if not coords:
+            pass
+        else:
+            L.append(f"{ind}{{ i64 r = {rowvar};")
+            for k in range(no - 1, -1, -1):
+                if k == 0:
+                    L.append(f"{ind}  xo{b}[0] = (int)r;")
+                else:
+                    L.append(f"{ind}  xo{b}[{k}] = (int)(r % {ext[k]}); r /= {ext[k]};")
+            L.append(f"{ind}}}")
+            for ci, cls in enumerate(cond_cls):
+                if cls == "outer":
+                    L.append(f"{ind}cr{b}_{ci} = {G.cond_expr(ci, names_r(b))};")
+            if "mixed" in cond_cls:
+                L.append(f"{ind}#pragma unroll")
+                L.append(f"{ind}for (int c = 0; c < C_; ++c) {{")
+                for ci, cls in enumerate(cond_cls):
+                    if cls == "mixed":
+                        L.append(f"{ind}  cm{b}_[c][{ci}] = {G.cond_expr(ci, names_i(b))};")
+                L.append(f"{ind}}}")
+        for k in scalars if scal else []:
             lf = P.leaves[k]
             g = " && ".join([f"cr{b}_{ci}" for ci in lf.guard]) or "true"
             L.append(f"{ind}s{b}_{k} = ({g}) ? ld1_{modes[k][1]}(P.in[{G.slot[k]}].ptr, {G.leaf_offset(k, names_r(b))}) : 0.f;")
-        for k in per_row:
-            L.extend(load_full(k, b, ind, f"w{b}_{k}" if k in packed else f"v{b}_{k}"))
+        for k in per_row if full else []:
+            if slot is None:
+                L.extend(load_full(k, b, ind, f"w{b}_{k}" if k in packed else f"v{b}_{k}"))
+                continue
+            lf = P.leaves[k]
+            es, ptr = _ES[modes[k][1]], f"P.in[{G.slot[k]}].ptr"
+            g = " && ".join(["lc[c]"] + [cref(ci, b) for ci in lf.guard])
+            L.append(f"{ind}#pragma unroll")
+            L.append(f"{ind}for (int c = 0; c < C_; ++c) {{")
+            L.append(f"{ind}  const bool ok_ = {g};")
+            L.append(f"{ind}  const char* src_ = (const char*){ptr} + (ok_ ? (i64)({G.leaf_offset(k, names_i(b))}) * {es} : (i64)0);")
+            for j in range(ring_n16[k]):
+                L.append(f"{ind}  cpa16(ring_ + ((i64)({slot}) * {ring_units} + {ring_base[k]} + c * {ring_n16[k]} + {j}) * {block} + threadIdx.x, src_ + {16 * j}, ok_);")
+            L.append(f"{ind}}}")
 
     def needed_for(targets):
         """Values that vary inside the row and must be evaluated in the element loop to produce `targets`."""
@@ -1661,7 +1761,17 @@ def generate_row(P: Program, modes: tuple) -> str:
                     if o.kind == "full":
                         L.append(f"{ind2}  float o{k}[W_];")
                 used = {P.ssa[i][4] for i in need if P.ssa[i][0] == "leaf"}
-                for k in sorted(used & packed):
+                for k in sorted(used & set(per_row)) if ring else []:
+                    unit = lambda j, k=k: f"st_[({ring_base[k]} + c * {ring_n16[k]} + {j}) * {block}]"
+                    if k in packed:
+                        L.append(f"{ind2}  V4 z{k} = {unit(0)}; asm volatile(\"\" : \"+r\"(z{k}.x), \"+r\"(z{k}.y), \"+r\"(z{k}.z), \"+r\"(z{k}.w));")
+                    else:
+                        L.append(f"{ind2}  float zf{k}[W_];")
+                        for j in range(ring_n16[k]):
+                            per = 16 // _ES[modes[k][1]]
+                            assert modes[k][1] == "f32"
+                            L.append(f"{ind2}  {{ const V4 a_ = {unit(j)}; zf{k}[{per * j}] = __uint_as_float(a_.x); zf{k}[{per * j + 1}] = __uint_as_float(a_.y); zf{k}[{per * j + 2}] = __uint_as_float(a_.z); zf{k}[{per * j + 3}] = __uint_as_float(a_.w); }}")
+                for k in sorted(used & packed) if not ring else []:
                     # a fresh copy per phase that the compiler cannot relate to the other phases' copies: the operand
                     # stays packed across the reduction instead of being kept unpacked (twice the registers)
                     L.append(f"{ind2}  V4 z{k} = w{b}_{k}[c]; asm volatile(\"\" : \"+r\"(z{k}.x), \"+r\"(z{k}.y), \"+r\"(z{k}.z), \"+r\"(z{k}.w));")
@@ -1707,7 +1817,41 @@ def generate_row(P: Program, modes: tuple) -> str:
 
     L.append(f"  const i64 STEP = (i64)gridDim.x * {RPC};")
     L.append(f"  i64 row = (i64)blockIdx.x * {RPC} + rslot;")
-    if nbuf == 1:
+    if ring:
+        D = NB - 1
+        L.append("  #pragma unroll")
+        L.append(f"  for (int j = 0; j < {D}; ++j) {{  // the first {D} rows of this thread are on their way before any is used")
+        L.append("    const i64 rp = row + j * STEP;")
+        L.append(f"    if (rp < {NR}) {{")
+        emit_load(1, "rp", "      ", scal=False, slot="j")
+        L.append("    }")
+        L.append("    cpa_commit();")
+        L.append("  }")
+        if scalars:
+            L.append(f"  if (row < {NR}) {{")
+            emit_load(1, "row", "    ", full=False)
+            L.append("  }")
+        L.append("  int slot = 0;")
+        L.append(f"  for (; row < {NR}; row += STEP) {{")
+        L.append(f"    {{ const i64 rp = row + {D} * STEP;  // refill the stage consumed one row ago")
+        L.append(f"      if (rp < {NR}) {{")
+        emit_load(1, "rp", "        ", scal=False, slot=f"(slot == 0 ? {D} : slot - 1)")
+        L.append("      }")
+        L.append("      cpa_commit();")
+        L.append("    }")
+        if scalars:
+            for k in scalars:
+                L.append(f"    s0_{k} = s1_{k};")
+            L.append(f"    {{ const i64 rn = row + STEP; if (rn < {NR}) {{")
+            emit_load(1, "rn", "      ", full=False)
+            L.append("    } }")
+        L.append(f"    cpa_wait<{D}>();  // this row's copies (the oldest group) have landed")
+        emit_load(0, "row", "    ", scal=False, full=False)
+        L.append(f"    const V4* st_ = ring_ + (i64)slot * {ring_units * block} + threadIdx.x;")
+        emit_body(0, "row", "    ")
+        L.append(f"    slot = slot == {D} ? 0 : slot + 1;")
+        L.append("  }")
+    elif nbuf == 1:
         L.append(f"  for (; row < {NR}; row += STEP) {{")
         emit_load(0, "row", "    ")
         emit_body(0, "row", "    ")
@@ -1775,12 +1919,15 @@ _klock = threading.Lock()
 
 
 class _Kernel:
-    def __init__(self, cubin: bytes, has_fold: bool):
+    def __init__(self, cubin: bytes, has_fold: bool, smem: int = 0):
         from cuda.bindings import driver
 
         self.driver = driver
+        self.smem = int(smem)  # dynamic shared memory of rk_main (the row kernels' staging ring)
         (self.module,) = jit._check(driver.cuModuleLoadData(cubin), "cuModuleLoadData")
         (self.main,) = jit._check(driver.cuModuleGetFunction(self.module, b"rk_main"), "cuModuleGetFunction")
+        if self.smem:
+            jit._check(driver.cuFuncSetAttribute(self.main, driver.CUfunction_attribute.CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, self.smem), "cuFuncSetAttribute")
         self.fold = jit._check(driver.cuModuleGetFunction(self.module, b"rk_fold"), "cuModuleGetFunction")[0] if has_fold else None
         self.launches = 0
         self._occ: dict = {}
@@ -1798,14 +1945,14 @@ class _Kernel:
         not a whole number of resident waves leaves part of the GPU idle for the last one."""
         if block not in self._occ:
             try:
-                (n,) = jit._check(self.driver.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.main, block, 0), "cuOccupancyMaxActiveBlocksPerMultiprocessor")
+                (n,) = jit._check(self.driver.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.main, block, self.smem), "cuOccupancyMaxActiveBlocksPerMultiprocessor")
                 self._occ[block] = max(1, int(n))
             except Exception:
                 self._occ[block] = 4
         return self._occ[block]
 
     def launch(self, func, params, grid, block, stream):
-        jit.fast_launch(self.driver, func, grid, block, stream, ctypes.addressof(params))
+        jit.fast_launch(self.driver, func, grid, block, stream, ctypes.addressof(params), self.smem if func is self.main else 0)
         self.launches += 1
 
 
@@ -1824,12 +1971,13 @@ def flat_unroll(P: Program) -> int:
     return 4 if n <= 2 else (2 if n <= 5 else 1)
 
 
-def source_for(P: Program, modes: tuple, min_ctas: int = 0) -> str:
-    return generate_flat(P, modes, flat_unroll(P), min_ctas) if P.kind == "flat" else generate_row(P, modes)
+def source_for(P: Program, modes: tuple, min_ctas: int = 0, ring: bool = True) -> str:
+    return generate_flat(P, modes, flat_unroll(P), min_ctas) if P.kind == "flat" else generate_row(P, modes, ring)
 
 
-def _get_kernel(P: Program, modes: tuple, dev_index: int) -> _Kernel:
-    key = (P.signature, modes, dev_index)
+def _get_kernel(P: Program, modes: tuple, dev_index: int, ring: bool = True) -> _Kernel:
+    ring = bool(ring and P.kind == "row" and row_ring(P, modes)[0])
+    key = (P.signature, modes, dev_index, ring)
     k = _kernels.get(key)
     if k is None:
         with _klock:
@@ -1846,7 +1994,7 @@ def _get_kernel(P: Program, modes: tuple, dev_index: int) -> _Kernel:
                                 k = cand
                                 break
                     if k is None:
-                        k = _Kernel(jit.compile_cubin(source_for(P, modes)), any(o.kind == "col" for o in P.outputs))
+                        k = _Kernel(jit.compile_cubin(source_for(P, modes, ring=ring)), any(o.kind == "col" for o in P.outputs), row_ring(P, modes)[2] if ring else 0)
                 _kernels[key] = k
     return k
 
@@ -1888,6 +2036,7 @@ class RegionLaunch:
         self.in_names, self.slot = input_slots(self.P)
         self.Params = _params_type(len(self.in_names), len(self.P.outputs))
         self._plans: dict = {}
+        self.tuned: dict = {}  # plan key -> (ms in registers, ms through the ring) where both were timed
         self.kind = "b200k_region[row]" if self.P.kind == "row" else "b200k_region[gather]"
 
     def run(self, env: dict) -> dict:
@@ -1919,22 +2068,45 @@ class RegionLaunch:
                 if P.in_shapes is not None and tuple(t.shape) != tuple(P.in_shapes[name]):
                     raise RuntimeError(f"b200ex region: operand {name} has shape {tuple(t.shape)}, the region was traced for {P.in_shapes[name]}")
             modes = leaf_modes(P, [tensors[s] for s in self.slot])
-            kernel = _get_kernel(P, modes, dev.index)
-            prm = self.Params()
             sms = _sm_count()
-            if P.kind == "flat":
-                U = flat_unroll(P)
-                items = math.prod(P.ext) // P.W
-                geo = (max(1, min((items + 256 * U - 1) // (256 * U), sms * min(_GRID_CTAS, kernel.ctas_per_sm(256)))), 256, 0, 0)
-            else:
-                T, C, RPC, block = row_geometry(P)
-                ncol = sum(1 for o in P.outputs if o.kind == "col")
-                groups = (P.n_rows + RPC - 1) // RPC
-                grid = max(1, min(groups, sms * kernel.ctas_per_sm(block)))
-                geo = (grid, block, grid * RPC if ncol else 0, ncol * grid * RPC * P.row_len)
-            plan = (kernel, prm, threading.Lock(), geo)
+
+            def make_plan(kernel):
+                if P.kind == "flat":
+                    U = flat_unroll(P)
+                    items = math.prod(P.ext) // P.W
+                    geo = (max(1, min((items + 256 * U - 1) // (256 * U), sms * min(_GRID_CTAS, kernel.ctas_per_sm(256)))), 256, 0, 0)
+                else:
+                    T, C, RPC, block = row_geometry(P)
+                    ncol = sum(1 for o in P.outputs if o.kind == "col")
+                    groups = (P.n_rows + RPC - 1) // RPC
+                    grid = max(1, min(groups, sms * kernel.ctas_per_sm(block)))
+                    geo = (grid, block, grid * RPC if ncol else 0, ncol * grid * RPC * P.row_len)
+                return (kernel, self.Params(), threading.Lock(), geo)
+
+            plan = None
+            if P.kind == "row" and row_ring(P, modes)[0] and _RING_MODE != "1":
+                plan = make_plan(_get_kernel(P, modes, dev.index, ring=False))
+                if _RING_MODE == "auto" and not torch.cuda.is_current_stream_capturing():
+                    # Two builds of the same arithmetic — rows staged through the shared-memory ring, or prefetched one
+                    # row ahead in registers.  Which wins depends on whether the row's critical path or the bytes in
+                    # flight bound the kernel (measured both ways on B200), so the first call times them on its own
+                    # operands and keeps the faster; the results are bit-identical either way.
+                    other = make_plan(_get_kernel(P, modes, dev.index, ring=True))
+                    t_reg, t_ring = (self._time_plan(pl, tensors, outs, dev) for pl in (plan, other))
+                    self.tuned[key] = (t_reg, t_ring)
+                    if t_ring < t_reg:
+                        plan = other
+            if plan is None:
+                plan = make_plan(_get_kernel(P, modes, dev.index))
             if len(self._plans) < self.MAX_PLANS:
                 self._plans[key] = plan
+        self._launch_plan(plan, tensors, outs, dev)
+        return result
+
+    def _launch_plan(self, plan, tensors, outs, dev):
+        from .ops import _on
+
+        P = self.P
         kernel, prm, lock, (grid, block, nparts, scratch_elems) = plan
         stream = torch.cuda.current_stream(dev).cuda_stream
         scratch = torch.empty(scratch_elems, dtype=torch.float32, device=dev) if scratch_elems else None
@@ -1949,4 +2121,16 @@ class RegionLaunch:
             kernel.launch(kernel.main, prm, grid, block, stream)
             if scratch is not None:
                 kernel.launch(kernel.fold, prm, (P.row_len + 31) // 32, 256, stream)
-        return result
+
+    def _time_plan(self, plan, tensors, outs, dev, reps: int = 3) -> float:
+        """Milliseconds per launch of `plan` on the caller's operands (one warm-up, then `reps` launches between two
+        events on the current stream).  The launches write the region's real outputs; they are idempotent."""
+        with torch.cuda.device(dev):
+            self._launch_plan(plan, tensors, outs, dev)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                self._launch_plan(plan, tensors, outs, dev)
+            b.record()
+            b.synchronize()
+            return a.elapsed_time(b) / reps
