@@ -82,9 +82,20 @@ def test_reference_qkv_split_rope_one_region_each_way(n_head, groups, hs, rope_n
     assert_bit_equal(res)
 
 
+@pytest.fixture(params=["auto", "1", "0"])
+def staging(request, monkeypatch):
+    """How row kernels stage their rows: through the cp.async ring in shared memory ("1"), prefetched in registers
+    ("0"), or whichever the first call measures faster ("auto", the default).  The arithmetic is the same; every row
+    test runs all three so that a fault in the build that loses the timing cannot hide."""
+    from b200ex import regionc
+
+    monkeypatch.setattr(regionc, "_RING_MODE", request.param)
+    return request.param
+
+
 @pytest.mark.parametrize("dtype", [BF, F32])
 @pytest.mark.parametrize("rows,hidden", [(64, 256), (33, 96), (8192, 4096), (5, 8200)])
-def test_hand_spelled_rmsnorm_with_residual(dtype, rows, hidden):
+def test_hand_spelled_rmsnorm_with_residual(staging, dtype, rows, hidden):
     """litgpt.model.RMSNorm spelled with torch ops: one row kernel forward, one backward (dx plus the weight
     gradient's column sum folded from per-CTA partials)."""
     g = torch.Generator(device=DEV).manual_seed(0)
@@ -102,7 +113,7 @@ def test_hand_spelled_rmsnorm_with_residual(dtype, rows, hidden):
     assert_reduction_close(res)
 
 
-def test_llama2_rmsnorm():
+def test_llama2_rmsnorm(staging):
     g = torch.Generator(device=DEV).manual_seed(0)
     x, w = torch.randn(4, 128, 512, generator=g, device=DEV).to(BF), torch.randn(512, generator=g, device=DEV)
     res = run_both(llama2_rmsnorm, [x, w])
@@ -111,7 +122,7 @@ def test_llama2_rmsnorm():
     assert_reduction_close(res)
 
 
-def test_hand_spelled_row_reductions():
+def test_hand_spelled_row_reductions(staging):
     g = torch.Generator(device=DEV).manual_seed(0)
     x = torch.randn(6, 40, 1000, generator=g, device=DEV)
     w, b = torch.randn(1000, generator=g, device=DEV), torch.randn(1000, generator=g, device=DEV)
