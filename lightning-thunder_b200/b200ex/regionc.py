@@ -1464,13 +1464,20 @@ def _leaf_sids(P: Program) -> dict:
     return {s[4]: i for i, s in enumerate(P.ssa) if s[0] == "leaf"}
 
 
-def row_geometry(P: Program):
+def row_geometry(P: Program, staged: bool = False):
     """(threads per row, chunks per thread, rows per CTA, block size).  A row lives in the registers of T threads,
-    each owning C interleaved chunks of W elements; the more operands stay resident, the fewer chunks per thread."""
+    each owning C interleaved chunks of W elements; the more operands stay resident, the fewer chunks per thread.
+    staged: the per-row operands wait in the shared-memory ring (row_ring), so only the row-independent operands and
+    the column accumulators (which also bring the most arithmetic: counted twice) hold registers — measured: the
+    LayerNorm forward at 4 chunks x 128 threads 25.7 us against 28.0 us at 2 x 256, while kernels with column sums
+    spill there and lose."""
     R, W = P.row_len, P.W
     items = (R + W - 1) // W
     sid = _leaf_sids(P)
-    resident = sum(1 for k in range(len(P.leaves)) if P.full[sid[k]]) + sum(1 for o in P.outputs if o.kind == "col")
+    ncols = sum(1 for o in P.outputs if o.kind == "col")
+    resident = sum(1 for k in range(len(P.leaves)) if P.full[sid[k]]) + ncols
+    if staged:
+        resident = len(_row_operands(P)[0]) + 2 * ncols
     cmax = 4 if resident <= 2 else (2 if resident <= 5 else 1)
     if resident > 5:
         # many operands, but 16-bit ones stay packed (4 registers per 8 elements): two chunks per thread still fit
@@ -1509,11 +1516,12 @@ def _row_operands(P: Program):
 
 
 _ES = {"bf16": 2, "f16": 2, "f32": 4}
-# B200EX_ROW_RING: "auto" (default: time both builds on the first call), "1" (always the ring), "0" (never)
+# B200EX_ROW_RING: "auto" (default: time the builds on the first call), "1" (always the ring, widest geometry), "v1" (the
+# ring at the register geometry), "0" (never)
 _RING_MODE = os.environ.get("B200EX_ROW_RING", "auto")
 
 
-def row_ring(P: Program, modes: tuple):
+def row_ring(P: Program, modes: tuple, staged: bool = True):
     """(stages, 16-byte units per thread and stage, dynamic shared-memory bytes) of the row kernel's staging ring, or
     (0, 0, 0) when the kernel keeps its rows in registers.
 
@@ -1525,7 +1533,7 @@ def row_ring(P: Program, modes: tuple):
     if _RING_MODE == "0" or P.kind != "row":
         return 0, 0, 0
     hoisted, per_row, _ = _row_operands(P)
-    T, C, RPC, block = row_geometry(P)
+    T, C, RPC, block = row_geometry(P, staged=staged)
     cols = sum(1 for o in P.outputs if o.kind == "col")
     nph = max(P.phase) + 1
     if not per_row or not (len(per_row) >= 3 or cols or nph >= 3):
@@ -1544,7 +1552,7 @@ def row_ring(P: Program, modes: tuple):
     return nb, units, nb * stage
 
 
-def generate_row(P: Program, modes: tuple, use_ring: bool = True) -> str:
+def generate_row(P: Program, modes: tuple, variant: int = 2) -> str:
     """Row-persistent kernel.  One row lives in the registers of T threads (a warp, or a whole CTA), C interleaved
     chunks of W elements per thread.  16-bit operands stay packed (one 16-byte register quad per chunk) and are
     unpacked where they are used, which halves their register cost and pays for a second buffer: the next row's loads
@@ -1554,7 +1562,11 @@ def generate_row(P: Program, modes: tuple, use_ring: bool = True) -> str:
     in_names, G.slot = input_slots(P)
     W, ext, nv, no = P.W, P.ext, len(P.ext), P.n_outer
     R, NR = P.row_len, P.n_rows
-    T, C, RPC, block = row_geometry(P)
+    # variant 0: rows prefetched in registers; 1: staged through the ring at the register geometry; 2: ring with the
+    # geometry that assumes the per-row operands hold no registers (row_geometry(staged=True))
+    NB, ring_units, _ = row_ring(P, modes, variant == 2) if variant else (0, 0, 0)
+    ring = NB > 0
+    T, C, RPC, block = row_geometry(P, staged=ring and variant == 2)
     cols = [k for k, o in enumerate(P.outputs) if o.kind == "col"]
     nph = max(P.phase) + 1
     reduces = [i for i, s in enumerate(P.ssa) if s[0].startswith("reduce_")]
@@ -1580,8 +1592,6 @@ def generate_row(P: Program, modes: tuple, use_ring: bool = True) -> str:
     # a two-operand single-reduction row (RMSNorm forward) is already at the HBM limit without it
     worth = len(per_row) >= 3 or bool(cols) or nph >= 3
     nbuf = 2 if (worth and 2 * cost + fixed <= 150 and os.environ.get("B200EX_ROW_PREFETCH", "1") != "0") else 1
-    NB, ring_units, _ = row_ring(P, modes) if use_ring else (0, 0, 0)
-    ring = NB > 0
     if ring:
         nbuf = 1  # rows wait in shared memory, not in a second set of registers
         # 16-byte unit of (leaf k, chunk c, part j) inside a stage: unit index * block + threadIdx.x
@@ -1590,7 +1600,7 @@ def generate_row(P: Program, modes: tuple, use_ring: bool = True) -> str:
             ring_n16[k] = W * _ES[modes[k][1]] // 16
             ring_base[k] = u_
             u_ += C * ring_n16[k]
-    G.packed_math = nbuf == 1 and not (ring and len(per_row) + len(hoisted) + len(cols) > 4)
+    G.packed_math = nbuf == 1  # float2 arithmetic where no second register buffer competes for the registers
 
     names_i = lambda b: [f"xo{b}[{k}]" for k in range(no)] + [f"xi[c][{k - no}]" for k in range(no, nv)]
     names_r = lambda b: [f"xo{b}[{k}]" for k in range(no)] + ["0"] * n_inner
@@ -1941,6 +1951,7 @@ class _Kernel:
 
         self.driver = driver
         self.smem = int(smem)  # dynamic shared memory of rk_main (the row kernels' staging ring)
+        self.variant = 0
         (self.module,) = jit._check(driver.cuModuleLoadData(cubin), "cuModuleLoadData")
         (self.main,) = jit._check(driver.cuModuleGetFunction(self.module, b"rk_main"), "cuModuleGetFunction")
         if self.smem:
@@ -1988,13 +1999,28 @@ def flat_unroll(P: Program) -> int:
     return 4 if n <= 2 else (2 if n <= 5 else 1)
 
 
-def source_for(P: Program, modes: tuple, min_ctas: int = 0, ring: bool = True) -> str:
-    return generate_flat(P, modes, flat_unroll(P), min_ctas) if P.kind == "flat" else generate_row(P, modes, ring)
+def source_for(P: Program, modes: tuple, min_ctas: int = 0, variant: int = 2) -> str:
+    return generate_flat(P, modes, flat_unroll(P), min_ctas) if P.kind == "flat" else generate_row(P, modes, variant)
 
 
-def _get_kernel(P: Program, modes: tuple, dev_index: int, ring: bool = True) -> _Kernel:
-    ring = bool(ring and P.kind == "row" and row_ring(P, modes)[0])
-    key = (P.signature, modes, dev_index, ring)
+def row_variants(P: Program, modes: tuple) -> list:
+    """Builds of a row program worth timing against each other (see generate_row): [0] alone when the ring does not
+    apply, else 0, 1 and — where it gives another geometry — 2."""
+    if P.kind != "row" or not row_ring(P, modes, False)[0]:
+        return [0]
+    out = [0, 1]
+    if row_ring(P, modes, True)[0] and row_geometry(P, True) != row_geometry(P, False):
+        out.append(2)
+    return out
+
+
+def _get_kernel(P: Program, modes: tuple, dev_index: int, variant: int = -1) -> _Kernel:
+    if P.kind != "row":
+        variant = 0
+    elif variant < 0 or variant not in row_variants(P, modes):
+        vs = row_variants(P, modes)
+        variant = 0 if _RING_MODE == "0" else (1 if (_RING_MODE == "v1" and 1 in vs) else vs[-1])
+    key = (P.signature, modes, dev_index, variant)
     k = _kernels.get(key)
     if k is None:
         with _klock:
@@ -2011,7 +2037,9 @@ def _get_kernel(P: Program, modes: tuple, dev_index: int, ring: bool = True) -> 
                                 k = cand
                                 break
                     if k is None:
-                        k = _Kernel(jit.compile_cubin(source_for(P, modes, ring=ring)), any(o.kind == "col" for o in P.outputs), row_ring(P, modes)[2] if ring else 0)
+                        k = _Kernel(jit.compile_cubin(source_for(P, modes, variant=variant)), any(o.kind == "col" for o in P.outputs),
+                                    row_ring(P, modes, variant == 2)[2] if variant else 0)
+                        k.variant = variant
                 _kernels[key] = k
     return k
 
@@ -2093,7 +2121,7 @@ class RegionLaunch:
                     items = math.prod(P.ext) // P.W
                     geo = (max(1, min((items + 256 * U - 1) // (256 * U), sms * min(_GRID_CTAS, kernel.ctas_per_sm(256)))), 256, 0, 0)
                 else:
-                    T, C, RPC, block = row_geometry(P)
+                    T, C, RPC, block = row_geometry(P, staged=kernel.variant == 2)
                     ncol = sum(1 for o in P.outputs if o.kind == "col")
                     groups = (P.n_rows + RPC - 1) // RPC
                     grid = max(1, min(groups, sms * kernel.ctas_per_sm(block)))
@@ -2101,18 +2129,20 @@ class RegionLaunch:
                 return (kernel, self.Params(), threading.Lock(), geo)
 
             plan = None
-            if P.kind == "row" and row_ring(P, modes)[0] and _RING_MODE != "1":
-                plan = make_plan(_get_kernel(P, modes, dev.index, ring=False))
+            variants = row_variants(P, modes) if _RING_MODE != "0" else [0]
+            if len(variants) > 1 and _RING_MODE not in ("1", "v1"):
+                plan = make_plan(_get_kernel(P, modes, dev.index, 0))
                 if _RING_MODE == "auto" and not torch.cuda.is_current_stream_capturing():
-                    # Two builds of the same arithmetic — rows staged through the shared-memory ring, or prefetched one
-                    # row ahead in registers.  Which wins depends on whether the row's critical path or the bytes in
-                    # flight bound the kernel (measured both ways on B200), so the first call times them on its own
-                    # operands and keeps the faster; the results are bit-identical either way.
-                    other = make_plan(_get_kernel(P, modes, dev.index, ring=True))
-                    t_reg, t_ring = (self._time_plan(pl, tensors, outs, dev) for pl in (plan, other))
-                    self.tuned[key] = (t_reg, t_ring)
-                    if t_ring < t_reg:
-                        plan = other
+                    # Builds of the same arithmetic — rows prefetched one ahead in registers, or staged through the
+                    # shared-memory ring (at the register geometry, or with more chunks per thread).  Which wins
+                    # depends on whether the row's critical path, its register budget or the bytes in flight bound
+                    # the kernel (all three happen, measured on B200), so the first call times them on its own operands
+                    # and keeps the fastest.  Every build sums in the same order per geometry; results differ at most
+                    # by the reassociation of the row sums.
+                    plans = [plan] + [make_plan(_get_kernel(P, modes, dev.index, v)) for v in variants[1:]]
+                    times = [self._time_plan(pl, tensors, outs, dev) for pl in plans]
+                    self.tuned[key] = dict(zip(variants, times))
+                    plan = plans[times.index(min(times))]
             if plan is None:
                 plan = make_plan(_get_kernel(P, modes, dev.index))
             if len(self._plans) < self.MAX_PLANS:

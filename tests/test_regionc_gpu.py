@@ -82,10 +82,11 @@ def test_reference_qkv_split_rope_one_region_each_way(n_head, groups, hs, rope_n
     assert_bit_equal(res)
 
 
-@pytest.fixture(params=["auto", "1", "0"])
+@pytest.fixture(params=["auto", "1", "v1", "0"])
 def staging(request, monkeypatch):
-    """How row kernels stage their rows: through the cp.async ring in shared memory ("1"), prefetched in registers
-    ("0"), or whichever the first call measures faster ("auto", the default).  The arithmetic is the same; every row
+    """How row kernels stage their rows: through the cp.async ring in shared memory ("1": with the geometry that
+    assumes it, "v1": at the register geometry), prefetched in registers ("0"), or whichever the first call measures
+    fastest ("auto", the default).  The arithmetic is the same; every row
     test runs all three so that a fault in the build that loses the timing cannot hide."""
     from b200ex import regionc
 
