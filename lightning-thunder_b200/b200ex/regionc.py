@@ -1942,6 +1942,7 @@ def _params_type(n_in, n_out):
 
 
 _kernels: dict = {}
+_choice: dict = {}  # (program signature, leaf modes, device) -> build chosen by the first call's timing
 _klock = threading.Lock()
 
 
@@ -2139,10 +2140,16 @@ class RegionLaunch:
                     # the kernel (all three happen, measured on B200), so the first call times them on its own operands
                     # and keeps the fastest.  Every build sums in the same order per geometry; results differ at most
                     # by the reassociation of the row sums.
-                    plans = [plan] + [make_plan(_get_kernel(P, modes, dev.index, v)) for v in variants[1:]]
-                    times = [self._time_plan(pl, tensors, outs, dev) for pl in plans]
-                    self.tuned[key] = dict(zip(variants, times))
-                    plan = plans[times.index(min(times))]
+                    ckey = (P.signature, modes, dev.index)
+                    best = _choice.get(ckey)  # the same program in another region (every layer of a model) is timed once
+                    if best is None:
+                        plans = [plan] + [make_plan(_get_kernel(P, modes, dev.index, v)) for v in variants[1:]]
+                        times = [self._time_plan(pl, tensors, outs, dev) for pl in plans]
+                        self.tuned[key] = dict(zip(variants, times))
+                        best = _choice[ckey] = variants[times.index(min(times))]
+                        plan = plans[variants.index(best)]
+                    elif best != 0:
+                        plan = make_plan(_get_kernel(P, modes, dev.index, best))
             if plan is None:
                 plan = make_plan(_get_kernel(P, modes, dev.index))
             if len(self._plans) < self.MAX_PLANS:

@@ -450,21 +450,27 @@ rmsnorm_bwd_tma_kernel(const T* __restrict__ dy, const T* __restrict__ h, const 
                     if constexpr (!(kHasDhIn && kIsF32)) o[e] = __fadd2_rn(__fadd2_rn(o[e], hs), hs);
                     if constexpr (kHasW) dwacc[i][e] = __fadd2_rn(dwacc[i][e], V::rnd2f(__fmul2_rn(__fmul2_rn(hf[e], rstd2), dyf[e])));
                 }
-                if constexpr (kHasDhIn) {
+                if constexpr (kHasDhIn && kIsF32) {
                     float2 df[kP];
                     V::unpack2(div[r][i], df);
 #pragma unroll
                     for (int e = 0; e < kP; ++e) {
-                        if constexpr (kIsF32) {
-                            // fp32 has no rounding boundary: the reference accumulates dh_in first
-                            const float2 hs = __fmul2_rn(hf[e], sc2);
-                            o[e] = __fadd2_rn(__fadd2_rn(__fadd2_rn(df[e], o[e]), hs), hs);
-                        } else {
-                            o[e] = __fadd2_rn(df[e], V::rnd2f(o[e]));
-                        }
+                        // fp32 has no rounding boundary: the reference accumulates dh_in first
+                        const float2 hs = __fmul2_rn(hf[e], sc2);
+                        o[e] = __fadd2_rn(__fadd2_rn(__fadd2_rn(df[e], o[e]), hs), hs);
                     }
                 }
-                st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, V::pack2(o));
+                if constexpr (kHasDhIn && !kIsF32) {
+                    // 16-bit: round(dh_in + round(o)) is one packed convert and one packed add on the words as loaded
+                    // (the packed add rounds the exact sum once, which equals the fp32 add followed by the rounding)
+                    const uint32_t dw_[4] = {div[r][i].x, div[r][i].y, div[r][i].z, div[r][i].w};
+                    uint32_t ow[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+                    for (int e = 0; e < kP; ++e) ow[e] = Pk<T>::add(dw_[e], V::pack_word(o[e]));
+                    st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, make_uint4(ow[0], ow[1], ow[2], ow[3]));
+                } else {
+                    st_stream(reinterpret_cast<uint4*>(dx) + row * nvec + tid + i * nc, V::pack2(o));
+                }
             }
         }
     }

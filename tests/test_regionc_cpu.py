@@ -106,8 +106,10 @@ def compiles(programs):
             t.dtype = lf.dtype
             ts.append(t)
         modes = regionc.leaf_modes(P, ts)
-        cubin = jit.compile_cubin(regionc.source_for(P, modes))
-        assert len(cubin) > 1000
+        # every build of a row program (register prefetch, cp.async ring at either geometry) must compile
+        for variant in regionc.row_variants(P, modes) if P.kind == "row" else [0]:
+            cubin = jit.compile_cubin(regionc.source_for(P, modes, variant=variant))
+            assert len(cubin) > 1000
 
 
 from ref_models import litgpt_rmsnorm, llama2_rmsnorm, qkv_split_rope  # noqa: E402
@@ -242,3 +244,29 @@ def test_unsupported_layouts_decline_but_keep_the_elementwise_part(_cpu_claiming
     fn = lambda x: (x * 2.0)[:, 1:].reshape(9, 6) + 1.0  # [6, 9] -> [9, 6]: digits do not line up
     res = run_both(fn, [x])
     assert_same(res, exact=False, rtol=1e-6, atol=1e-6)
+
+
+def test_row_constant_factors_leave_the_row_sums(_cpu_claiming):
+    """sum(s * y) = s * sum(y) for s constant along the row: the hand-spelled LayerNorm backward then needs ONE pass
+    over the row for its sums (every reduction in phase 0) instead of two with a barrier in between, and its builds
+    include the shared-memory ring (16-bit operands, three phases' worth of work)."""
+    torch.manual_seed(0)
+    x = torch.randn(16, 512).to(BF)
+    w, b = torch.randn(512).to(BF), torch.randn(512).to(BF)
+
+    def ln(x, w, b):
+        xf = x.float()
+        mu = xf.mean(-1, keepdim=True)
+        var = ((xf - mu) ** 2).mean(-1, keepdim=True)
+        return ((xf - mu) * torch.rsqrt(var + 1e-5) * w.float() + b.float()).to(x.dtype)
+
+    res = run_both(ln, [x, w, b])
+    o, g, _ = res["torch"]
+    for got, want in zip(res["b200"][0] + res["b200"][1], o + g):
+        torch.testing.assert_close(got.float(), want.float(), rtol=1.6e-2, atol=float(want.float().abs().max()) * 2.0**-8)
+    bwd = [P for P in _cpu_claiming if P.kind == "row" and any(o.kind == "col" for o in P.outputs)]
+    assert len(bwd) == 1
+    P = bwd[0]
+    reduces = [i for i, s_ in enumerate(P.ssa) if s_[0].startswith("reduce_")]
+    assert len(reduces) == 3 and all(P.phase[P.ssa[i][1]] == 0 for i in reduces), [(P.ssa[i], P.phase[i]) for i in reduces]
+    compiles(_cpu_claiming)
