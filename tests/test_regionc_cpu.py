@@ -251,7 +251,7 @@ def test_row_constant_factors_leave_the_row_sums(_cpu_claiming):
     over the row for its sums (every reduction in phase 0) instead of two with a barrier in between, and its builds
     include the shared-memory ring (16-bit operands, three phases' worth of work)."""
     torch.manual_seed(0)
-    x = torch.randn(16, 512).to(BF)
+    x = torch.randn(64, 512).to(BF)
     w, b = torch.randn(512).to(BF), torch.randn(512).to(BF)
 
     def ln(x, w, b):
