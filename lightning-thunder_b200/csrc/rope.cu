@@ -355,109 +355,6 @@ rope_bwd_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __r
     }
 }
 
-// n / d and n % d for n < 2^31 by one multiply-high and a shift (d, mul, shr from make_fastdiv on the host): the
-// index decomposition of a work item has five of them with run-time divisors.
-struct FastDiv {
-    uint32_t d, mul, shr;
-};
-FastDiv make_fastdiv(uint32_t d) {
-    if (d <= 1) return FastDiv{1u, 0u, 0u};
-    uint32_t lg = 0;
-    while ((1ull << lg) < d) ++lg;
-    const uint32_t p = 31 + lg;
-    return FastDiv{d, static_cast<uint32_t>(((1ull << p) + d - 1) / d), p - 32};
-}
-__device__ __forceinline__ uint32_t fd_div(uint32_t n, const FastDiv& f) { return f.d == 1 ? n : __umulhi(n, f.mul) >> f.shr; }
-
-struct RopeBwdDivs {
-    FastDiv vph, slots, G, T;
-};
-
-// Backward for 16-bit storage with 16-byte vectors, one OUTPUT vector of dqkv per thread.  Thread order: vector p
-// within the head row fastest, then 16 consecutive tokens, then slot / group / token tile — a CTA of 256 threads is
-// one (slot, group) over 16 tokens, so there is no divergence, the head-major cotangents are read in 4 KB runs and the
-// token-major result is written in 256-byte pieces.  A q slot is one source head; a k / v slot folds the q_per_kv
-// expanded copies (fp32 sum of the rounded per-copy results, one rounding, as the expand's vjp does).  Both rotary
-// halves have the same form on packed words: out = rnd(cos[own] * g[own]) +/- rnd(sin[partner] * g[partner]).
-// Few registers (all loads of a thread are issued before the first is used: at most 2 * kBwdChunk vectors), index
-// arithmetic in 32 bits with multiply-high divisions.
-template <typename T, int kMinBlocks>
-__global__ void __launch_bounds__(256, kMinBlocks)
-rope_bwd_vec16_kernel(const T* __restrict__ dq, const T* __restrict__ dk, const T* __restrict__ dv, const T* __restrict__ cosp,
-                      const T* __restrict__ sinp, T* __restrict__ dqkv, RopeShape s, RopeBwdDivs dv_, uint32_t nitems) {
-    using K = Pk<T>;
-    constexpr int kW = 8;
-    const int half = s.rope_n / 2 / kW;
-    const int slots = s.qpk + 2;
-    const int hkv = s.expand ? s.G * s.qpk : s.G;
-    const int nq = s.G * s.qpk;
-    const uint32_t ntok = static_cast<uint32_t>(s.B * s.T);
-    for (uint32_t item = blockIdx.x * 256u + threadIdx.x; item < nitems; item += gridDim.x * 256u) {
-        uint32_t r = fd_div(item, dv_.vph);
-        const int p = static_cast<int>(item - r * dv_.vph.d);
-        const uint32_t tt = r % kTokTile;
-        r /= kTokTile;
-        uint32_t q = fd_div(r, dv_.slots);
-        const int slot = static_cast<int>(r - q * dv_.slots.d);
-        r = q;
-        q = fd_div(r, dv_.G);
-        const int g = static_cast<int>(r - q * dv_.G.d);
-        const uint32_t bt = q * kTokTile + tt;
-        if (bt >= ntok) continue;
-        const uint32_t b = fd_div(bt, dv_.T), t = bt - b * dv_.T.d;
-        const bool is_q = slot < s.qpk, is_v = slot == s.qpk + 1;
-        const bool roped = p < 2 * half && !is_v;
-        const bool low = p < half;
-        const int e_own = p * kW, e_par = (low ? p + half : p - half) * kW;
-        const T* base = is_q ? dq : (is_v ? dv : dk);
-        const int heads_total = is_q ? nq : hkv;
-        const int nsrc = is_q ? 1 : (s.expand ? s.qpk : 1);
-        const int head0 = is_q ? g * s.qpk + slot : (s.expand ? g * s.qpk : g);
-        uint4 c = make_uint4(0u, 0u, 0u, 0u), sn = c;
-        if (roped) {
-            c = ld_keep(cosp + static_cast<int64_t>(t) * s.rope_n + e_own);
-            sn = ld_keep(sinp + static_cast<int64_t>(t) * s.rope_n + e_par);
-            if (!low) sn = make_uint4(sn.x ^ 0x80008000u, sn.y ^ 0x80008000u, sn.z ^ 0x80008000u, sn.w ^ 0x80008000u);  // a - b = a + (-b)
-        }
-        T* dst = dqkv + ((static_cast<int64_t>(bt) * s.G + g) * slots + slot) * s.hs + e_own;
-        float acc[kW];
-#pragma unroll
-        for (int e = 0; e < kW; ++e) acc[e] = 0.f;
-        for (int s0 = 0; s0 < nsrc; s0 += kBwdChunk) {
-            uint4 own[kBwdChunk], par[kBwdChunk];
-#pragma unroll
-            for (int j = 0; j < kBwdChunk; ++j) {
-                if (s0 + j < nsrc) {
-                    const T* src = base + ((static_cast<int64_t>(b) * heads_total + head0 + s0 + j) * s.T + t) * s.hs;
-                    own[j] = ld_stream(src + e_own);
-                    if (roped) par[j] = ld_stream(src + e_par);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < kBwdChunk; ++j) {
-                if (s0 + j < nsrc) {
-                    uint4 d = own[j];
-                    if (roped) {
-                        // rnd(rnd(cos * g_own) +/- rnd(sin_partner * g_partner)); sin carries the sign
-                        d.x = K::add(K::mul(c.x, own[j].x), K::mul(sn.x, par[j].x));
-                        d.y = K::add(K::mul(c.y, own[j].y), K::mul(sn.y, par[j].y));
-                        d.z = K::add(K::mul(c.z, own[j].z), K::mul(sn.z, par[j].z));
-                        d.w = K::add(K::mul(c.w, own[j].w), K::mul(sn.w, par[j].w));
-                    }
-                    if (nsrc == 1) {
-                        st_stream(dst, d);
-                    } else {
-                        float f[kW];
-                        Vec<T>::unpack(d, f);
-#pragma unroll
-                        for (int e = 0; e < kW; ++e) acc[e] += f[e];
-                    }
-                }
-            }
-        }
-        if (nsrc > 1) st_stream(dst, Vec<T>::pack(acc));
-    }
-}
 // B200K_ROPE_PACKED=0 selects the fp32 form for 16-bit storage (bit-for-bit comparison in the tests).
 bool packed_enabled() {
     static const bool on = [] {
@@ -493,39 +390,6 @@ int run(bool fwd, const void* a0, const void* a1, const void* a2, const void* co
             kernel_bwd<<<grid, 128, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
                                              static_cast<const T*>(cosp), static_cast<const T*>(sinp), static_cast<T*>(o0), s, nitems);
     };
-    if constexpr (kE == 8) {
-        // 16-bit backward: one output vector per thread (rope_bwd_vec16_kernel); B200K_ROPE_BWD_VEC=0 keeps the
-        // (token, group, pass) kernel for A/B runs
-        static const bool vec16 = [] {
-            const char* e = getenv("B200K_ROPE_BWD_VEC");
-            return !(e != nullptr && e[0] == '0');
-        }();
-        const int64_t tiles = (s.B * s.T + kTokTile - 1) / kTokTile;
-        const int64_t n16 = tiles * kTokTile * s.G * (s.qpk + 2) * (s.hs / kE);
-        if (!fwd && vec && packed_enabled() && vec16 && n16 < (int64_t{1} << 31) && s.B * s.T < (int64_t{1} << 31)) {
-            const RopeBwdDivs dv{make_fastdiv(static_cast<uint32_t>(s.hs / kE)), make_fastdiv(static_cast<uint32_t>(s.qpk + 2)),
-                                 make_fastdiv(static_cast<uint32_t>(s.G)), make_fastdiv(static_cast<uint32_t>(s.T))};
-            const int64_t want16 = (n16 + 255) / 256;
-            static const int minb = [] {
-                const char* e = getenv("B200K_ROPE_BWD_MINB");
-                return e != nullptr && e[0] == '3' ? 3 : 2;
-            }();
-            static const int per_sm = [] {
-                const char* e = getenv("B200K_ROPE_BWD_CTAS");
-                return e != nullptr && e[0] != 0 ? atoi(e) : 0;
-            }();
-            const int64_t cap16 = static_cast<int64_t>(sm_count()) * (per_sm > 0 ? per_sm : minb);
-            const int grid16 = static_cast<int>(want16 < cap16 ? want16 : cap16);
-            auto go16 = [&](auto kernel) {
-                kernel<<<grid16, 256, 0, st>>>(static_cast<const T*>(a0), static_cast<const T*>(a1), static_cast<const T*>(a2),
-                                               static_cast<const T*>(cosp), static_cast<const T*>(sinp), static_cast<T*>(o0), s, dv,
-                                               static_cast<uint32_t>(n16));
-            };
-            if (minb == 3) go16(rope_bwd_vec16_kernel<T, 3>);
-            else go16(rope_bwd_vec16_kernel<T, 2>);
-            return launch_status();
-        }
-    }
     if (vec && kE == 8 && packed_enabled()) launch(rope_fwd_kernel<T, kE, (kE == 8)>, rope_bwd_kernel<T, kE, (kE == 8)>);
     else if (vec) launch(rope_fwd_kernel<T, kE, false>, rope_bwd_kernel<T, kE, false>);
     else launch(rope_fwd_kernel<T, 1, false>, rope_bwd_kernel<T, 1, false>);
