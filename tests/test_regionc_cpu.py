@@ -270,3 +270,47 @@ def test_row_constant_factors_leave_the_row_sums(_cpu_claiming):
     reduces = [i for i, s_ in enumerate(P.ssa) if s_[0].startswith("reduce_")]
     assert len(reduces) == 3 and all(P.phase[P.ssa[i][1]] == 0 for i in reduces), [(P.ssa[i], P.phase[i]) for i in reduces]
     compiles(_cpu_claiming)
+
+
+def test_row_ring_plan_fits_the_sm(_cpu_claiming):
+    """The staging ring of a row kernel (regionc.row_ring) is planned on the host: its shared memory must leave room for
+    the CTAs per SM the launch bounds promise (200 KB split between them), it needs at least two stages, and the
+    builds offered to the first-call timing start with the register build (the one used under stream capture)."""
+    torch.manual_seed(0)
+    x = torch.randn(64, 4096).to(BF)
+    w, b = torch.randn(4096).to(BF), torch.randn(4096).to(BF)
+
+    def ln(x, w, b):
+        xf = x.float()
+        mu = xf.mean(-1, keepdim=True)
+        var = ((xf - mu) ** 2).mean(-1, keepdim=True)
+        return ((xf - mu) * torch.rsqrt(var + 1e-5) * w.float() + b.float()).to(x.dtype)
+
+    run_both(ln, [x, w, b])
+    rows = [P for P in _cpu_claiming if P.kind == "row"]
+    assert rows
+    seen_ring = False
+    for P in rows:
+        class _T:
+            def __init__(self, shape, dt):
+                self.shape, self.dtype, self._st, acc = shape, dt, [0] * len(shape), 1
+                for i in range(len(shape) - 1, -1, -1):
+                    self._st[i] = acc
+                    acc *= shape[i]
+
+            def stride(self, i):
+                return self._st[i]
+
+            def data_ptr(self):
+                return 0
+
+        modes = regionc.leaf_modes(P, [_T(P.in_shapes[lf.name], lf.dtype) for lf in P.leaves])
+        variants = regionc.row_variants(P, modes)
+        assert variants[0] == 0
+        for v in variants[1:]:
+            seen_ring = True
+            stages, units, smem = regionc.row_ring(P, modes, v == 2)
+            T, C, RPC, block = regionc.row_geometry(P, staged=v == 2)
+            assert stages >= 2 and smem == stages * units * block * 16
+            assert smem * max(1, 512 // block) <= 200 * 1024
+    assert seen_ring, "a 4096-wide bf16 LayerNorm should offer the ring"
