@@ -1698,9 +1698,7 @@ def generate_row(P: Program, modes: tuple, variant: int = 2) -> str:
     def emit_load(b, rowvar, ind, coords=True, scal=True, full=True, slot=None):
         """coords: the row's outer coordinates and conditions into set b; scal: its scalars; full: its operands — into
         registers, or (slot given) into ring stage `slot` with cp.async."""
-        if not coords:
-            pass
-        else:
+        if coords:
             L.append(f"{ind}{{ i64 r = {rowvar};")
             for k in range(no - 1, -1, -1):
                 if k == 0:
